@@ -1,0 +1,110 @@
+"""Host-side forest container in xgboost's wire format and its scoring
+entry point.  Mirrors the parts of ``xgboost.Booster`` the reference touches:
+``get_booster().get_score(importance_type='gain')`` (src/api/cobalt_fast_api.py:135-136),
+``feature_names`` and prediction behind ``predict_proba`` (src/api/cobalt_fast_api.py:91)."""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+
+from . import _lib, ops
+
+_FIELDS = ("left", "right", "parent", "split_index", "split_cond", "default_left", "base_weight", "loss_chg",
+           "sum_hess")
+
+
+def base_margin_of(base_score: float) -> float:
+    p = float(base_score)
+    return float(np.float32(-math.log(1.0 / p - 1.0)))
+
+
+def pack_forest(tree_offsets, left, right, split_index, split_cond, default_left):
+    """Wire-format arrays -> packed 8-byte nodes for cb_predict.
+    node = cond bits | meta << 32; meta = feature | default_left << 15 | left_child << 16 (0 = leaf)."""
+    left = np.asarray(left, np.int64)
+    right = np.asarray(right, np.int64)
+    internal = left >= 0
+    if np.any(right[internal] != left[internal] + 1):
+        raise _lib.CobaltError("forest nodes must allocate children consecutively (right = left + 1)")
+    sizes = np.diff(np.asarray(tree_offsets, np.int64))
+    if sizes.size and sizes.max() > 65535:
+        raise _lib.CobaltError("a tree has more than 65535 nodes")
+    feat = np.asarray(split_index, np.int64)
+    if internal.any() and feat[internal].max() > 32767:
+        raise _lib.CobaltError("feature index above 32767")
+    meta = np.where(internal, feat | (np.asarray(default_left, np.int64) << 15) | (left << 16), 0).astype(np.uint64)
+    cond = np.ascontiguousarray(split_cond, np.float32).view(np.uint32).astype(np.uint64)
+    nodes = (cond | (meta << np.uint64(32))).astype(np.uint64)
+    return nodes.view(np.int64), np.asarray(tree_offsets, np.int32)
+
+
+class Booster:
+    def __init__(self, forest: dict, n_features: int, feature_names=None, base_score: float = 0.5,
+                 attributes: dict | None = None):
+        self.forest = {k: np.ascontiguousarray(forest[k]) for k in _FIELDS if k in forest}
+        self.forest["tree_offsets"] = np.asarray(forest["tree_offsets"], np.int64)
+        if "split_bin" in forest:
+            self.forest["split_bin"] = np.ascontiguousarray(forest["split_bin"])
+        self.n_features = int(n_features)
+        self.feature_names = list(feature_names) if feature_names is not None else None
+        self.base_score = float(base_score)
+        self.attributes = dict(attributes or {})
+        self._dev_cache = {}
+
+    # ---- pickling: host arrays only (no CUDA state crosses process boundaries)
+    def __getstate__(self):
+        d = dict(self.__dict__)
+        d["_dev_cache"] = {}
+        return d
+
+    def num_boosted_rounds(self) -> int:
+        return len(self.forest["tree_offsets"]) - 1
+
+    def num_features(self) -> int:
+        return self.n_features
+
+    def _names(self):
+        return self.feature_names if self.feature_names is not None else [f"f{i}" for i in range(self.n_features)]
+
+    def get_score(self, fmap: str = "", importance_type: str = "weight") -> dict:
+        """Per-feature importance; features never split on are omitted (xgboost semantics, R12)."""
+        fo = self.forest
+        internal = fo["left"] >= 0
+        feat = fo["split_index"][internal].astype(np.int64)
+        cnt = np.bincount(feat, minlength=self.n_features).astype(np.float64)
+        gain = np.bincount(feat, weights=fo["loss_chg"][internal].astype(np.float64), minlength=self.n_features)
+        cover = np.bincount(feat, weights=fo["sum_hess"][internal].astype(np.float64), minlength=self.n_features)
+        if importance_type == "weight":
+            val = cnt
+        elif importance_type == "gain":
+            val = np.divide(gain, cnt, out=np.zeros_like(gain), where=cnt > 0)
+        elif importance_type == "total_gain":
+            val = gain
+        elif importance_type == "cover":
+            val = np.divide(cover, cnt, out=np.zeros_like(cover), where=cnt > 0)
+        elif importance_type == "total_cover":
+            val = cover
+        else:
+            raise ValueError(f"Unknown importance type: {importance_type}")
+        names = self._names()
+        return {names[j]: float(val[j]) for j in range(self.n_features) if cnt[j] > 0}
+
+    def _device_forest(self, device):
+        key = str(device)
+        if key not in self._dev_cache:
+            fo = self.forest
+            nodes, toff = pack_forest(fo["tree_offsets"], fo["left"], fo["right"], fo["split_index"], fo["split_cond"],
+                                      fo["default_left"])
+            self._dev_cache[key] = (torch.from_numpy(nodes).to(device), torch.from_numpy(toff).to(device))
+        return self._dev_cache[key]
+
+    def predict_device(self, X: torch.Tensor, output_margin: bool = False) -> torch.Tensor:
+        """X: CUDA f32 [n, n_features].  Returns p (or the margin) as a CUDA f32 [n] tensor."""
+        if X.shape[1] != self.n_features:
+            raise ValueError(f"Feature shape mismatch, expected: {self.n_features}, got {X.shape[1]}")
+        nodes, toff = self._device_forest(X.device)
+        m, p = ops.predict(X, nodes, toff, base_margin_of(self.base_score), want_margin=output_margin,
+                           want_proba=not output_margin)
+        return m if output_margin else p

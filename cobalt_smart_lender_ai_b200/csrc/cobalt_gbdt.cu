@@ -1,0 +1,560 @@
+// libcobalt_gbdt.so -- C ABI over the sm_100a kernels (see include/cobalt_gbdt.h).
+#include <new>
+
+#include "sketch.cuh"
+#include "trainer.cuh"
+
+namespace cb {
+thread_local char g_err[512] = "";
+
+int device_info(DeviceInfo* out) {
+  int dev = 0;
+  CB_CUDA(cudaGetDevice(&dev));
+  static thread_local DeviceInfo cache;
+  if (cache.device != dev) {
+    CB_CUDA(cudaDeviceGetAttribute(&cache.sm_count, cudaDevAttrMultiProcessorCount, dev));
+    CB_CUDA(cudaDeviceGetAttribute(&cache.smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    cache.device = dev;
+  }
+  *out = cache;
+  return CB_OK;
+}
+
+static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+// shared-memory budget of hist_accum in histogram slots (8 bytes per slot)
+static inline int hist_budget_slots(const DeviceInfo& di) { return (di.smem_optin - 2048) / 8; }
+static inline int hist_tiles_bound(int S, int budget) {
+  int eff = budget - 4 * CB_MAX_BINS;
+  int t = (S + eff - 1) / eff;
+  return t < 1 ? 1 : t;
+}
+static inline int64_t max_partials(int64_t rows, int grid) { return (rows + kChunkRows - 1) / kChunkRows + 2 * (int64_t)grid + kMaxBuild; }
+
+static int launch_hist_accum(const uint8_t* bins, int64_t ldb, const int32_t* gpair, const uint32_t* row_idx,
+                             int identity, const HistPlan* plan, const int32_t* bin_ptr, int f, int S, int grid,
+                             int n_tiles_bound, int smem_bytes, int32_t* partials, cudaStream_t s) {
+  static thread_local int attr_dev = -1, attr_smem = 0;
+  int dev = 0;
+  CB_CUDA(cudaGetDevice(&dev));
+  if (attr_dev != dev || attr_smem < smem_bytes) {
+    CB_CUDA(cudaFuncSetAttribute(hist_accum_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    attr_dev = dev; attr_smem = smem_bytes;
+  }
+  dim3 g(grid, n_tiles_bound);
+  hist_accum_kernel<4><<<g, 1024, smem_bytes, s>>>(reinterpret_cast<const uint32_t*>(bins), (int)(ldb / 4),
+                                                   reinterpret_cast<const int2*>(gpair), row_idx, identity, plan,
+                                                   bin_ptr, f, S, partials);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+}  // namespace cb
+
+using namespace cb;
+
+extern "C" {
+
+int cb_version(void) { return CB_VERSION; }
+const char* cb_last_error(void) { return g_err; }
+
+int cb_device_info(int* sm_count, int* smem_optin_bytes) {
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  if (sm_count) *sm_count = di.sm_count;
+  if (smem_optin_bytes) *smem_optin_bytes = di.smem_optin;
+  return CB_OK;
+}
+
+// ---------------------------------------------------------------------------- K2
+int cb_bin_pack_u8(const float* X, int64_t n, int f, int64_t ldx, const float* cuts, const int32_t* n_cuts,
+                   uint8_t* bins, int64_t ldb, void* stream) {
+  if (!X || !cuts || !n_cuts || !bins || n < 0 || f <= 0 || ldx < f || ldb < f || (ldb & 3))
+    return fail(CB_ERR_INVALID, "cb_bin_pack_u8: bad arguments (ldb must be a multiple of 4 and >= n_features)");
+  if (n == 0) return CB_OK;
+  int wpr = (int)(ldb / 4);
+  int64_t items = n * wpr;
+  bin_pack_kernel<<<ceil_div(items, 256), 256, 0, (cudaStream_t)stream>>>(X, n, f, ldx, cuts, n_cuts,
+                                                                         reinterpret_cast<uint32_t*>(bins), wpr);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+// ---------------------------------------------------------------------------- K3
+int cb_grad_logistic_q(const float* margin, const uint8_t* y, const float* weight, int64_t n, float spw, int sg,
+                       int sh, uint32_t keep_thresh, uint32_t seed, uint32_t tree, int64_t row_offset,
+                       int32_t* gpair, int64_t* totals, void* stream) {
+  if (!margin || !y || !gpair || !totals || n < 0) return fail(CB_ERR_INVALID, "cb_grad_logistic_q: bad arguments");
+  if (n == 0) return CB_OK;
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  int grid = (int)std::min<int64_t>(ceil_div(n, 256), (int64_t)di.sm_count * 8);
+  grad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(margin, y, weight, n, spw, ldexpf(1.0f, sg), ldexpf(1.0f, sh),
+                                                      keep_thresh, seed, tree, row_offset,
+                                                      reinterpret_cast<int2*>(gpair),
+                                                      reinterpret_cast<unsigned long long*>(totals));
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+int cb_sigmoid(const float* margin, int64_t n, float* out, void* stream) {
+  if (!margin || !out || n < 0) return fail(CB_ERR_INVALID, "cb_sigmoid: bad arguments");
+  if (n == 0) return CB_OK;
+  sigmoid_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(margin, n, out);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+// ---------------------------------------------------------------------------- K4
+int cb_hist_workspace_bytes(int64_t max_rows, int total_bins, size_t* bytes) {
+  if (!bytes || max_rows < 0 || total_bins <= 0) return fail(CB_ERR_INVALID, "cb_hist_workspace_bytes: bad arguments");
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  Bump b(nullptr);
+  b.take<HistPlan>(1);
+  b.take<int32_t>((size_t)max_partials(max_rows, di.sm_count) * 2 * total_bins);
+  *bytes = b.used();
+  return CB_OK;
+}
+
+int cb_hist_build(const uint8_t* bins, int64_t ldb, int f, const int32_t* gpair, const uint32_t* row_idx,
+                  int64_t count, const int32_t* bin_ptr, int total_bins, int64_t* hist, void* ws, size_t ws_bytes,
+                  void* stream) {
+  if (!bins || !gpair || !bin_ptr || !hist || !ws || f <= 0 || total_bins <= 0 || count < 0 || (ldb & 3) ||
+      count > 2147483647LL)
+    return fail(CB_ERR_INVALID, "cb_hist_build: bad arguments");
+  size_t need = 0;
+  int rc = cb_hist_workspace_bytes(count, total_bins, &need);
+  if (rc) return rc;
+  if (ws_bytes < need) return fail(CB_ERR_WORKSPACE, "cb_hist_build: workspace %zu < %zu bytes", ws_bytes, need);
+  DeviceInfo di;
+  device_info(&di);
+  cudaStream_t s = (cudaStream_t)stream;
+  Bump b(ws);
+  HistPlan* plan = b.take<HistPlan>(1);
+  int32_t* partials = b.take<int32_t>((size_t)max_partials(count, di.sm_count) * 2 * total_bins);
+  const int budget = hist_budget_slots(di);
+  const int tiles = hist_tiles_bound(total_bins, budget);
+  if (tiles > kMaxTiles) return fail(CB_ERR_UNSUPPORTED, "cb_hist_build: %d bins need more than %d tiles", total_bins, kMaxTiles);
+  plan_tiles_kernel<<<1, 1, 0, s>>>(bin_ptr, f, budget, plan);
+  plan_single_kernel<<<1, 1, 0, s>>>(plan, (int)count, di.sm_count);
+  CB_LAUNCH_CHECK();
+  const int smem = std::min(budget, total_bins) * 8;
+  rc = launch_hist_accum(bins, ldb, gpair, row_idx, row_idx == nullptr, plan, bin_ptr, f, total_bins, di.sm_count,
+                         tiles, smem, partials, s);
+  if (rc) return rc;
+  hist_reduce_kernel<<<dim3(ceil_div(total_bins, 256), 1), 256, 0, s>>>(partials, plan, total_bins, hist);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+int cb_hist_subtract(const int64_t* parent, const int64_t* built, int64_t* sibling, int64_t n, void* stream) {
+  if (!parent || !built || !sibling || n < 0) return fail(CB_ERR_INVALID, "cb_hist_subtract: bad arguments");
+  if (n == 0) return CB_OK;
+  subtract_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(parent, built, sibling, n);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+// ---------------------------------------------------------------------------- K5
+}  // extern "C"
+
+namespace cb {
+__global__ void __launch_bounds__(128) scan_single_kernel(const int64_t* __restrict__ hist,
+                                                          const int32_t* __restrict__ bin_ptr, int f,
+                                                          const int64_t* __restrict__ totals, cb_tree_params p,
+                                                          const uint8_t* __restrict__ feature_mask,
+                                                          FeatBest* __restrict__ feat_best) {
+  const int feat = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (feat >= f) return;
+  FeatBest fb;
+  fb.chg = 0.0f; fb.split_bin = -1; fb.default_left = 0; fb.pad = 0; fb.GL = 0; fb.HL = 0;
+  if (!feature_mask || feature_mask[feat]) {
+    const int b0 = __ldg(bin_ptr + feat), nb = __ldg(bin_ptr + feat + 1) - b0;
+    fb = scan_feature(hist + 2 * (size_t)b0, nb, totals[0], totals[1], p);
+  }
+  if ((threadIdx.x & 31) == 0) feat_best[feat] = fb;
+}
+
+__global__ void pick_single_kernel(const FeatBest* __restrict__ feat_best, int f, const float* __restrict__ cuts,
+                                   const float* __restrict__ min_vals, const int64_t* __restrict__ totals,
+                                   cb_split* out) {
+  if (threadIdx.x || blockIdx.x) return;
+  float bc = 0.0f; int bf = -1;
+  for (int j = 0; j < f; ++j)
+    if (feat_best[j].chg > bc) { bc = feat_best[j].chg; bf = j; }
+  cb_split s;
+  memset(&s, 0, sizeof s);
+  s.feature = bf; s.loss_chg = bc;
+  if (bf >= 0) {
+    const FeatBest fb = feat_best[bf];
+    s.split_bin = fb.split_bin; s.default_left = fb.default_left;
+    s.threshold = fb.split_bin >= 0 ? cuts[(size_t)bf * CB_CUT_STRIDE + fb.split_bin] : min_vals[bf];
+    s.GL = fb.GL; s.HL = fb.HL; s.GR = totals[0] - fb.GL; s.HR = totals[1] - fb.HL;
+  }
+  *out = s;
+}
+}  // namespace cb
+
+extern "C" {
+
+int cb_split_scan_workspace_bytes(int f, size_t* bytes) {
+  if (!bytes || f <= 0) return fail(CB_ERR_INVALID, "cb_split_scan_workspace_bytes: bad arguments");
+  Bump b(nullptr);
+  b.take<FeatBest>((size_t)f);
+  *bytes = b.used();
+  return CB_OK;
+}
+
+int cb_split_scan(const int64_t* hist, const int32_t* bin_ptr, int f, const float* cuts, const float* min_vals,
+                  const int64_t* totals, const cb_tree_params* params, const uint8_t* feature_mask, cb_split* out,
+                  void* ws, size_t ws_bytes, void* stream) {
+  if (!hist || !bin_ptr || !cuts || !min_vals || !totals || !params || !out || !ws || f <= 0)
+    return fail(CB_ERR_INVALID, "cb_split_scan: bad arguments");
+  size_t need = 0;
+  cb_split_scan_workspace_bytes(f, &need);
+  if (ws_bytes < need) return fail(CB_ERR_WORKSPACE, "cb_split_scan: workspace %zu < %zu bytes", ws_bytes, need);
+  cudaStream_t s = (cudaStream_t)stream;
+  FeatBest* fbuf = Bump(ws).take<FeatBest>((size_t)f);
+  scan_single_kernel<<<ceil_div(f, 4), 128, 0, s>>>(hist, bin_ptr, f, totals, *params, feature_mask, fbuf);
+  pick_single_kernel<<<1, 1, 0, s>>>(fbuf, f, cuts, min_vals, totals, out);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+// ---------------------------------------------------------------------------- K6
+int cb_partition_workspace_bytes(int64_t count, size_t* bytes) {
+  if (!bytes || count < 0) return fail(CB_ERR_INVALID, "cb_partition_workspace_bytes: bad arguments");
+  Bump b(nullptr);
+  b.take<uint32_t>((size_t)(count / 32 + 2));
+  b.take<int>((size_t)(count / kPartTile + 2));
+  *bytes = b.used();
+  return CB_OK;
+}
+
+int cb_partition_stable(const uint8_t* bins, int64_t ldb, const uint32_t* seg_in, int64_t count, int feature,
+                        int split_bin, int default_left, uint32_t* seg_out, int64_t* n_left, void* ws,
+                        size_t ws_bytes, void* stream) {
+  if (!bins || !seg_in || !seg_out || !n_left || !ws || count < 0 || feature < 0 || feature >= ldb ||
+      count > 2147483647LL)
+    return fail(CB_ERR_INVALID, "cb_partition_stable: bad arguments");
+  size_t need = 0;
+  cb_partition_workspace_bytes(count, &need);
+  if (ws_bytes < need) return fail(CB_ERR_WORKSPACE, "cb_partition_stable: workspace %zu < %zu bytes", ws_bytes, need);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (count == 0) {
+    CB_CUDA(cudaMemsetAsync(n_left, 0, sizeof(int64_t), s));
+    return CB_OK;
+  }
+  Bump b(ws);
+  uint32_t* flag_bits = b.take<uint32_t>((size_t)(count / 32 + 2));
+  int* tile_cnt = b.take<int>((size_t)(count / kPartTile + 2));
+  const int nt = ceil_div(count, kPartTile);
+  part1_flags_kernel<<<nt, 256, 0, s>>>(bins, ldb, seg_in, count, feature, split_bin, default_left, flag_bits, tile_cnt);
+  part2_scan_kernel<<<1, 1024, 0, s>>>(tile_cnt, nt, n_left);
+  part3_scatter_kernel<<<nt, 256, 0, s>>>(seg_in, count, flag_bits, tile_cnt, n_left, seg_out);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+// ---------------------------------------------------------------------------- K8
+int cb_predict(const float* X, int64_t n, int f, int64_t ldx, const uint64_t* nodes, const int32_t* tree_off,
+               int n_trees, float base_margin, float* out_margin, float* out_proba, void* stream) {
+  if (!X || !nodes || !tree_off || n < 0 || f <= 0 || f > 32767 || ldx < f || n_trees < 0 || (!out_margin && !out_proba))
+    return fail(CB_ERR_INVALID, "cb_predict: bad arguments");
+  if (n == 0) return CB_OK;
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  const int smem = f * kPredRows * (int)sizeof(float);
+  if (smem > di.smem_optin)
+    return fail(CB_ERR_UNSUPPORTED, "cb_predict: %d features need %d bytes of shared memory (> %d)", f, smem, di.smem_optin);
+  static thread_local int attr_dev = -1, attr_smem = 0;
+  if (attr_dev != di.device || attr_smem < smem) {
+    CB_CUDA(cudaFuncSetAttribute(predict_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_dev = di.device; attr_smem = smem;
+  }
+  predict_kernel<<<ceil_div(n, kPredRows), kPredRows, smem, (cudaStream_t)stream>>>(
+      X, n, f, ldx, reinterpret_cast<const uint2*>(nodes), tree_off, n_trees, base_margin, out_margin, out_proba);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+// ---------------------------------------------------------------------------- trainer
+struct cb_trainer_s {
+  cb_train_config cfg;
+  cb_train_buffers buf;
+  DeviceInfo di;
+  int max_nodes, S, S2, grid, tiles, smem, n_part_tiles, pool_slots, lb_slots;
+  int2* gpair;
+  uint32_t* rows[2];
+  int cur;
+  bool identity;
+  uint32_t* flag_bits;
+  int* tile_cnt;
+  TreeState* st;
+  LevelSegs* segs;
+  HistPlan* plan;
+  NodeArrays na;
+  int64_t* pool;
+  int64_t* level_buf;
+  int32_t* partials;
+  FeatBest* feat_best;
+  int tree_index;
+  const uint8_t* fmask;
+  int64_t launches;
+  bool timing;
+  cudaEvent_t ev[3];
+};
+
+static int trainer_layout(const cb_train_config* cfg, const DeviceInfo& di, void* ws, cb_trainer_s* t, size_t* bytes) {
+  const int D = cfg->tree.max_depth;
+  const int64_t n = cfg->n_rows;
+  const int S = cfg->total_bins;
+  const int max_nodes = (1 << (D + 1)) - 1;
+  const int pool_slots = (1 << D) - 1;
+  const int lb_slots = D >= 2 ? (1 << (D - 2)) : 1;
+  const int lvl_nodes = 1 << (D - 1);
+  Bump b(ws);
+  int2* gpair = b.take<int2>((size_t)n);
+  uint32_t* r0 = b.take<uint32_t>((size_t)n);
+  uint32_t* r1 = b.take<uint32_t>((size_t)n);
+  uint32_t* flag_bits = b.take<uint32_t>((size_t)(n / 32 + 2));
+  int* tile_cnt = b.take<int>((size_t)(n / kPartTile + 2));
+  TreeState* st = b.take<TreeState>(1);
+  LevelSegs* segs = b.take<LevelSegs>(1);
+  HistPlan* plan = b.take<HistPlan>(1);
+  NodeArrays na;
+  na.begin = b.take<int>((size_t)max_nodes);
+  na.count = b.take<int>((size_t)max_nodes);
+  na.G = b.take<long long>((size_t)max_nodes);
+  na.H = b.take<long long>((size_t)max_nodes);
+  int64_t* pool = b.take<int64_t>((size_t)pool_slots * 2 * S);
+  int64_t* level_buf = b.take<int64_t>((size_t)lb_slots * 2 * S + 2);
+  int32_t* partials = b.take<int32_t>((size_t)max_partials(n, di.sm_count) * 2 * S);
+  FeatBest* feat_best = b.take<FeatBest>((size_t)lvl_nodes * cfg->n_features);
+  if (bytes) *bytes = b.used();
+  if (t) {
+    t->max_nodes = max_nodes; t->S = S; t->S2 = 2 * S; t->pool_slots = pool_slots; t->lb_slots = lb_slots;
+    t->gpair = gpair; t->rows[0] = r0; t->rows[1] = r1; t->flag_bits = flag_bits; t->tile_cnt = tile_cnt;
+    t->st = st; t->segs = segs; t->plan = plan; t->na = na; t->pool = pool; t->level_buf = level_buf;
+    t->partials = partials; t->feat_best = feat_best;
+  }
+  return CB_OK;
+}
+
+static int trainer_check_cfg(const cb_train_config* cfg) {
+  if (!cfg) return fail(CB_ERR_INVALID, "trainer: null config");
+  if (cfg->n_rows <= 0 || cfg->n_rows > 2147483647LL) return fail(CB_ERR_INVALID, "trainer: n_rows out of range");
+  if (cfg->n_features <= 0 || cfg->ldb < cfg->n_features || (cfg->ldb & 3))
+    return fail(CB_ERR_INVALID, "trainer: ldb must be a multiple of 4 and >= n_features");
+  if (cfg->tree.max_depth < 1 || cfg->tree.max_depth > kMaxDepth)
+    return fail(CB_ERR_UNSUPPORTED, "trainer: max_depth must be in [1, %d]", kMaxDepth);
+  if (cfg->total_bins <= 0 || cfg->total_bins > cfg->n_features * CB_MAX_BINS)
+    return fail(CB_ERR_INVALID, "trainer: total_bins out of range");
+  if (cfg->max_trees <= 0) return fail(CB_ERR_INVALID, "trainer: max_trees must be positive");
+  return CB_OK;
+}
+
+int cb_trainer_workspace_bytes(const cb_train_config* cfg, size_t* bytes) {
+  int rc = trainer_check_cfg(cfg);
+  if (rc) return rc;
+  if (!bytes) return fail(CB_ERR_INVALID, "cb_trainer_workspace_bytes: null output");
+  DeviceInfo di;
+  rc = device_info(&di);
+  if (rc) return rc;
+  return trainer_layout(cfg, di, nullptr, nullptr, bytes);
+}
+
+int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, void* ws, size_t ws_bytes,
+                      cb_trainer** out) {
+  int rc = trainer_check_cfg(cfg);
+  if (rc) return rc;
+  if (!buf || !ws || !out) return fail(CB_ERR_INVALID, "cb_trainer_create: null argument");
+  if (!buf->bins || !buf->y || !buf->margin || !buf->bin_ptr || !buf->cuts || !buf->min_vals || !buf->left ||
+      !buf->right || !buf->parent || !buf->split_index || !buf->split_bin || !buf->split_cond || !buf->default_left ||
+      !buf->base_weight || !buf->loss_chg || !buf->sum_hess || !buf->n_nodes)
+    return fail(CB_ERR_INVALID, "cb_trainer_create: a required buffer is null");
+  DeviceInfo di;
+  rc = device_info(&di);
+  if (rc) return rc;
+  size_t need = 0;
+  trainer_layout(cfg, di, nullptr, nullptr, &need);
+  if (ws_bytes < need) return fail(CB_ERR_WORKSPACE, "cb_trainer_create: workspace %zu < %zu bytes", ws_bytes, need);
+  cb_trainer_s* t = new (std::nothrow) cb_trainer_s();
+  if (!t) return fail(CB_ERR_INVALID, "cb_trainer_create: out of host memory");
+  t->cfg = *cfg; t->buf = *buf; t->di = di;
+  trainer_layout(cfg, di, ws, t, nullptr);
+  const int budget = hist_budget_slots(di);
+  t->tiles = hist_tiles_bound(t->S, budget);
+  if (t->tiles > kMaxTiles) { delete t; return fail(CB_ERR_UNSUPPORTED, "trainer: too many bins for %d tiles", kMaxTiles); }
+  t->smem = std::min(budget, t->S) * 8;
+  t->grid = std::min(di.sm_count, kMaxGrid);
+  t->n_part_tiles = ceil_div(cfg->n_rows, kPartTile);
+  t->cur = 0; t->identity = true; t->tree_index = 0; t->fmask = nullptr; t->launches = 0; t->timing = false;
+  plan_tiles_kernel<<<1, 1>>>(buf->bin_ptr, cfg->n_features, budget, t->plan);
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) { delete t; return fail(CB_ERR_CUDA, "cb_trainer_create: %s", cudaGetErrorString(e)); }
+  *out = t;
+  return CB_OK;
+}
+
+void cb_trainer_destroy(cb_trainer* tr) {
+  if (tr && tr->timing)
+    for (int i = 0; i < 3; ++i) cudaEventDestroy(tr->ev[i]);
+  delete tr;
+}
+
+int cb_trainer_enable_timing(cb_trainer* t, int on) {
+  if (!t) return fail(CB_ERR_INVALID, "trainer: null handle");
+  if (on && !t->timing) {
+    for (int i = 0; i < 3; ++i) CB_CUDA(cudaEventCreate(&t->ev[i]));
+    t->timing = true;
+  } else if (!on && t->timing) {
+    for (int i = 0; i < 3; ++i) cudaEventDestroy(t->ev[i]);
+    t->timing = false;
+  }
+  return CB_OK;
+}
+
+int cb_trainer_last_hist_timing_sync(cb_trainer* t, float* ms_accum, float* ms_reduce, int64_t* rows, int* n_build) {
+  if (!t || !t->timing) return fail(CB_ERR_INVALID, "trainer: timing is not enabled");
+  CB_CUDA(cudaEventSynchronize(t->ev[2]));
+  if (ms_accum) CB_CUDA(cudaEventElapsedTime(ms_accum, t->ev[0], t->ev[1]));
+  if (ms_reduce) CB_CUDA(cudaEventElapsedTime(ms_reduce, t->ev[1], t->ev[2]));
+  int h[2] = {0, 0};
+  CB_CUDA(cudaMemcpy(&h[0], &t->plan->n_build, sizeof(int), cudaMemcpyDeviceToHost));
+  CB_CUDA(cudaMemcpy(&h[1], &t->plan->total_rows, sizeof(int), cudaMemcpyDeviceToHost));
+  if (n_build) *n_build = h[0];
+  if (rows) *rows = h[1];
+  return CB_OK;
+}
+
+static TreeOut tree_out(cb_trainer_s* t) {
+  const size_t o = (size_t)t->tree_index * t->max_nodes;
+  TreeOut to;
+  to.left = t->buf.left + o; to.right = t->buf.right + o; to.parent = t->buf.parent + o;
+  to.split_index = t->buf.split_index + o; to.split_bin = t->buf.split_bin + o; to.split_cond = t->buf.split_cond + o;
+  to.default_left = t->buf.default_left + o; to.base_weight = t->buf.base_weight + o; to.loss_chg = t->buf.loss_chg + o;
+  to.sum_hess = t->buf.sum_hess + o;
+  return to;
+}
+
+int cb_trainer_round_begin(cb_trainer* t, int tree_index, const uint8_t* feature_mask, void* stream) {
+  if (!t) return fail(CB_ERR_INVALID, "trainer: null handle");
+  if (tree_index < 0 || tree_index >= t->cfg.max_trees) return fail(CB_ERR_INVALID, "trainer: tree_index %d out of range", tree_index);
+  cudaStream_t s = (cudaStream_t)stream;
+  t->tree_index = tree_index; t->fmask = feature_mask; t->identity = true; t->cur = 0;
+  const int64_t n = t->cfg.n_rows;
+  CB_CUDA(cudaMemsetAsync(t->st->root_tot, 0, 2 * sizeof(long long), s));
+  int g = (int)std::min<int64_t>(ceil_div(n, 256), (int64_t)t->di.sm_count * 8);
+  grad_kernel<<<g, 256, 0, s>>>(t->buf.margin, t->buf.y, t->buf.weight, n, t->cfg.scale_pos_weight,
+                                ldexpf(1.0f, t->cfg.tree.sg), ldexpf(1.0f, t->cfg.tree.sh), t->cfg.keep_thresh,
+                                t->cfg.seed, (uint32_t)tree_index, t->cfg.row_offset, t->gpair,
+                                reinterpret_cast<unsigned long long*>(t->st->root_tot));
+  round_init_kernel<<<ceil_div(t->max_nodes, 256), 256, 0, s>>>(t->st, t->na, tree_out(t), t->max_nodes, (int)n,
+                                                                t->plan, t->grid);
+  CB_LAUNCH_CHECK();
+  t->launches += 2;
+  return CB_OK;
+}
+
+int cb_trainer_level_hist(cb_trainer* t, int level, void* stream) {
+  if (!t || level < 0 || level >= t->cfg.tree.max_depth) return fail(CB_ERR_INVALID, "trainer: bad level");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
+  int rc = launch_hist_accum(t->cfg.n_rows ? t->buf.bins : nullptr, t->cfg.ldb, reinterpret_cast<const int32_t*>(t->gpair),
+                             t->rows[t->cur], t->identity ? 1 : 0, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S,
+                             t->grid, t->tiles, t->smem, t->partials, s);
+  if (rc) return rc;
+  if (t->timing) CB_CUDA(cudaEventRecord(t->ev[1], s));
+  const int nb = level == 0 ? 1 : (1 << (level - 1));
+  hist_reduce_kernel<<<dim3(ceil_div(t->S, 256), nb), 256, 0, s>>>(t->partials, t->plan, t->S, t->level_buf);
+  if (t->timing) CB_CUDA(cudaEventRecord(t->ev[2], s));
+  t->launches += 2;
+  if (level == 0) {
+    root_totals_kernel<<<1, 1, 0, s>>>(t->st, t->level_buf + t->S2);
+    t->launches += 1;
+  }
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+int cb_trainer_level_buffer(cb_trainer* t, int level, int64_t** ptr, int64_t* n_values) {
+  if (!t || level < 0 || level >= t->cfg.tree.max_depth || !ptr || !n_values) return fail(CB_ERR_INVALID, "trainer: bad level");
+  const int nb = level == 0 ? 1 : (1 << (level - 1));
+  *ptr = t->level_buf;
+  *n_values = (int64_t)nb * t->S2 + (level == 0 ? 2 : 0);
+  return CB_OK;
+}
+
+int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
+  if (!t || level < 0 || level >= t->cfg.tree.max_depth) return fail(CB_ERR_INVALID, "trainer: bad level");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int D = t->cfg.tree.max_depth;
+  const int nb = level == 0 ? 1 : (1 << (level - 1));
+  const int ln = 1 << level;
+  const int n = (int)t->cfg.n_rows;
+  hist_finalize_kernel<<<dim3(ceil_div(t->S2, 256), nb), 256, 0, s>>>(t->level_buf, t->plan, t->S2, t->pool, t->na,
+                                                                      level == 0 ? t->level_buf + t->S2 : nullptr);
+  scan_level_kernel<<<dim3(ceil_div(t->cfg.n_features, 4), ln), 128, 0, s>>>(
+      t->pool, t->buf.bin_ptr, t->cfg.n_features, t->S2, t->st, level, t->na, t->cfg.tree, t->fmask, t->feat_best);
+  level_finish_kernel<<<1, 256, 0, s>>>(t->st, level, D, t->feat_best, t->cfg.n_features, t->buf.cuts,
+                                        t->buf.min_vals, t->cfg.tree, t->na, tree_out(t), t->segs);
+  t->launches += 3;
+  const uint32_t* rin = t->rows[t->cur];
+  const int ident = t->identity ? 1 : 0;
+  if (level + 1 < D) {
+    uint32_t* rout = t->rows[t->cur ^ 1];
+    part_level_flags_kernel<<<t->n_part_tiles, 256, 0, s>>>(t->buf.bins, t->cfg.ldb, rin, ident, n, t->segs,
+                                                            t->flag_bits, t->tile_cnt);
+    part_level_scan_kernel<<<1, 1024, 0, s>>>(t->tile_cnt, t->n_part_tiles, n, t->flag_bits, t->segs, t->st, level, D,
+                                              t->na, t->plan, t->grid, t->cfg.world_size > 1 ? 1 : 0);
+    part_level_scatter_kernel<<<t->n_part_tiles, 256, 0, s>>>(rin, ident, n, t->segs, t->flag_bits, t->tile_cnt, rout,
+                                                              t->buf.margin);
+    t->cur ^= 1; t->identity = false;
+    t->launches += 3;
+  } else {
+    final_apply_kernel<<<ceil_div(n, 256), 256, 0, s>>>(t->buf.bins, t->cfg.ldb, rin, ident, n, t->segs, t->buf.margin);
+    t->launches += 1;
+  }
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+int cb_trainer_round_end(cb_trainer* t, void* stream) {
+  if (!t) return fail(CB_ERR_INVALID, "trainer: null handle");
+  round_end_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(t->st, t->buf.n_nodes + t->tree_index);
+  CB_LAUNCH_CHECK();
+  t->launches += 1;
+  return CB_OK;
+}
+
+int cb_trainer_boost_round(cb_trainer* t, int tree_index, const uint8_t* feature_mask, void* stream) {
+  int rc = cb_trainer_round_begin(t, tree_index, feature_mask, stream);
+  if (rc) return rc;
+  for (int level = 0; level < t->cfg.tree.max_depth; ++level) {
+    if ((rc = cb_trainer_level_hist(t, level, stream))) return rc;
+    if ((rc = cb_trainer_level_split(t, level, stream))) return rc;
+  }
+  return cb_trainer_round_end(t, stream);
+}
+
+int cb_trainer_row_order(cb_trainer* t, const uint32_t** ptr) {
+  if (!t || !ptr) return fail(CB_ERR_INVALID, "trainer: null argument");
+  *ptr = t->identity ? nullptr : t->rows[t->cur];
+  return CB_OK;
+}
+
+int cb_trainer_node_hist(cb_trainer* t, int node_id, const int64_t** ptr) {
+  if (!t || !ptr || node_id < 0 || node_id >= t->pool_slots) return fail(CB_ERR_INVALID, "trainer: node id out of range");
+  *ptr = t->pool + (size_t)node_id * t->S2;
+  return CB_OK;
+}
+
+int64_t cb_trainer_launch_count(cb_trainer* t) { return t ? t->launches : 0; }
+
+}  // extern "C"

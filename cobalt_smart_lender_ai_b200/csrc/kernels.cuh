@@ -1,0 +1,486 @@
+// Device kernels of the histogram-GBDT hot path (sm_100a).  Included by cobalt_gbdt.cu only.
+#pragma once
+#include "common.cuh"
+
+namespace cb {
+
+// =====================================================================================
+// K2  bin-index packing: one thread produces one u32 word = 4 features of one row
+// =====================================================================================
+__device__ __forceinline__ uint32_t bin_of(float x, const float* __restrict__ c, int nc) {
+  if (x != x) return CB_MISSING_BIN;
+  int lo = 0, hi = nc;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (__ldg(c + mid) <= x) lo = mid + 1; else hi = mid;
+  }
+  return (uint32_t)(lo == nc ? nc - 1 : lo);
+}
+
+__global__ void __launch_bounds__(256) bin_pack_kernel(const float* __restrict__ X, int64_t n, int f, int64_t ldx,
+                                                       const float* __restrict__ cuts,
+                                                       const int32_t* __restrict__ n_cuts,
+                                                       uint32_t* __restrict__ bins32, int wpr) {
+  int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (item >= n * wpr) return;
+  int64_t row = item / wpr;
+  int w = (int)(item - row * wpr);
+  const float* x = X + row * ldx;
+  uint32_t out = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    int feat = 4 * w + j;
+    uint32_t code = CB_MISSING_BIN;
+    if (feat < f) code = bin_of(__ldg(x + feat), cuts + (size_t)feat * CB_CUT_STRIDE, __ldg(n_cuts + feat));
+    out |= code << (8 * j);
+  }
+  bins32[item] = out;
+}
+
+// =====================================================================================
+// K3  logistic gradient / hessian, fixed point (R4)
+// =====================================================================================
+__global__ void __launch_bounds__(256) grad_kernel(const float* __restrict__ margin, const uint8_t* __restrict__ y,
+                                                   const float* __restrict__ weight, int64_t n, float spw,
+                                                   float fg, float fh, uint32_t keep_thresh, uint32_t seed,
+                                                   uint32_t tree, int64_t row_offset, int2* __restrict__ gpair,
+                                                   unsigned long long* __restrict__ totals) {
+  int64_t G = 0, H = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float p = spec_sigmoid(__ldg(margin + i));
+    uint8_t yi = __ldg(y + i);
+    float wt = yi ? spw : 1.0f;
+    if (weight) wt = __fmul_rn(wt, __ldg(weight + i));
+    float g = __fmul_rn(__fsub_rn(p, (float)yi), wt);
+    float hh = __fmul_rn(p, __fsub_rn(1.0f, p));
+    hh = hh < 1e-16f ? 1e-16f : hh;
+    float h = __fmul_rn(hh, wt);
+    int qg = (int)rintf(__fmul_rn(g, fg)), qh = (int)rintf(__fmul_rn(h, fh));
+    if (keep_thresh && spec_hash(seed, tree, (uint64_t)(row_offset + i)) >= keep_thresh) { qg = 0; qh = 0; }
+    gpair[i] = make_int2(qg, qh);
+    G += qg; H += qh;
+  }
+  G = warp_sum_i64(G); H = warp_sum_i64(H);
+  __shared__ int64_t sg[8], sh[8];
+  int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) { sg[wid] = G; sh[wid] = H; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int64_t a = 0, b = 0;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) { a += sg[k]; b += sh[k]; }
+    atomicAdd(totals, (unsigned long long)a);
+    atomicAdd(totals + 1, (unsigned long long)b);
+  }
+}
+
+__global__ void sigmoid_kernel(const float* __restrict__ m, int64_t n, float* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = spec_sigmoid(m[i]);
+}
+
+// =====================================================================================
+// K4  histogram build
+//   plan   : which CTA scans which slice of which node (device side, no host sync)
+//   accum  : shared-memory privatised int32 histograms, one partial per <= kChunkRows rows
+//   reduce : partials -> int64 level buffer
+// =====================================================================================
+struct TileInfo { int w0, w1, s0, s1; };  // u32 words [w0,w1) of a row, histogram slots [s0,s1)
+
+constexpr int kMaxTiles = 16;
+constexpr int kMaxBuild = 256;   // build nodes per level (depth <= 9)
+constexpr int kMaxGrid = 1024;   // CTAs along x in hist_accum
+
+struct HistPlan {               // lives in device memory
+  int n_tiles;
+  TileInfo tiles[kMaxTiles];
+  int n_build;
+  int total_rows;               // rows scanned by this level's build (sum over build nodes)
+  int b_node[kMaxBuild];        // node id whose histogram is built
+  int b_sibling[kMaxBuild];     // node id derived by subtraction (-1: none)
+  int b_parent[kMaxBuild];
+  int b_pbeg[kMaxBuild + 1];    // partial range of build slot j: [b_pbeg[j], b_pbeg[j+1])
+  int cta_slot[kMaxGrid];       // build slot of CTA b (-1: idle)
+  int cta_begin[kMaxGrid];      // first position (in row order) of the CTA's slice
+  int cta_rows[kMaxGrid];
+  int cta_pbase[kMaxGrid];      // first partial written by the CTA
+};
+
+// greedy feature tiling on u32-word boundaries; run once per bin layout
+__global__ void plan_tiles_kernel(const int32_t* __restrict__ bin_ptr, int f, int budget_slots, HistPlan* plan) {
+  if (threadIdx.x || blockIdx.x) return;
+  int words = (f + 3) / 4, nt = 0, w0 = 0, s0 = 0;
+  for (int w = 0; w < words; ++w) {
+    int e = bin_ptr[min(4 * w + 4, f)];
+    if (e - s0 > budget_slots && w > w0) {
+      if (nt < kMaxTiles) plan->tiles[nt] = TileInfo{w0, w, s0, bin_ptr[4 * w]};
+      ++nt; w0 = w; s0 = bin_ptr[4 * w];
+    }
+  }
+  if (nt < kMaxTiles) plan->tiles[nt] = TileInfo{w0, words, s0, bin_ptr[f]};
+  ++nt;
+  plan->n_tiles = min(nt, kMaxTiles);
+}
+
+// distributes `grid` CTAs over the build nodes proportionally to their row counts
+__device__ inline void plan_ctas(HistPlan* plan, int n_build, const int* begins, const int* counts, int grid) {
+  long long total = 0;
+  for (int j = 0; j < n_build; ++j) total += counts[j];
+  int spare = grid - n_build, b = 0, p = 0;
+  for (int j = 0; j < n_build; ++j) {
+    int nj = 1 + (total > 0 ? (int)((long long)spare * counts[j] / total) : 0);
+    int need = (counts[j] + kChunkRows - 1) / kChunkRows;   // no more CTAs than chunks
+    nj = max(1, min(nj, need));
+    int per = (counts[j] + nj - 1) / nj;
+    per = (per + 31) & ~31;
+    plan->b_pbeg[j] = p;
+    for (int k = 0; k < nj; ++k) {
+      int s = min(counts[j], k * per), e = min(counts[j], (k + 1) * per);
+      plan->cta_slot[b] = j; plan->cta_begin[b] = begins[j] + s; plan->cta_rows[b] = e - s; plan->cta_pbase[b] = p;
+      p += (e - s + kChunkRows - 1) / kChunkRows;
+      ++b;
+    }
+  }
+  plan->b_pbeg[n_build] = p;
+  plan->n_build = n_build;
+  plan->total_rows = (int)total;
+  for (; b < grid; ++b) { plan->cta_slot[b] = -1; plan->cta_rows[b] = 0; }
+}
+
+__global__ void plan_single_kernel(HistPlan* plan, int count, int grid) {
+  if (threadIdx.x || blockIdx.x) return;
+  int b0 = 0, c0 = count;
+  plan->b_node[0] = 0; plan->b_sibling[0] = -1; plan->b_parent[0] = -1;
+  plan_ctas(plan, 1, &b0, &c0, grid);
+}
+
+// blockDim.x = 1024.  Thread t owns u32 word (t % Wt) of rows (t / Wt) + k * RPB: its four
+// feature offsets are loop invariant, and within a warp every lane addresses a different
+// feature, so two lanes never hit the same histogram slot.
+template <int UNROLL>
+__global__ void __launch_bounds__(1024, 1)
+hist_accum_kernel(const uint32_t* __restrict__ bins32, int wpr, const int2* __restrict__ gpair,
+                  const uint32_t* __restrict__ row_idx, int identity, const HistPlan* __restrict__ plan,
+                  const int32_t* __restrict__ bin_ptr, int f, int S, int32_t* __restrict__ partials) {
+  extern __shared__ int32_t smem[];
+  const int tile_id = blockIdx.y;
+  if (tile_id >= plan->n_tiles) return;
+  const int slot = plan->cta_slot[blockIdx.x];
+  if (slot < 0) return;
+  const TileInfo tile = plan->tiles[tile_id];
+  const int St = tile.s1 - tile.s0, Wt = tile.w1 - tile.w0;
+  int32_t* sG = smem;
+  int32_t* sH = smem + St;
+  for (int s = threadIdx.x; s < 2 * St; s += blockDim.x) smem[s] = 0;
+  const int rpb = blockDim.x / Wt;
+  const int rl = threadIdx.x / Wt;
+  const int w = tile.w0 + (threadIdx.x - rl * Wt);
+  const bool active = rl < rpb;
+  int off[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    int feat = 4 * w + j;
+    off[j] = (active && feat < f) ? __ldg(bin_ptr + feat) - tile.s0 : 0;
+  }
+  __syncthreads();
+  const int pos0 = plan->cta_begin[blockIdx.x];
+  const int rows = plan->cta_rows[blockIdx.x];
+  int pid = plan->cta_pbase[blockIdx.x];
+  for (int c0 = 0; c0 < rows; c0 += kChunkRows, ++pid) {
+    const int crow = min(kChunkRows, rows - c0);
+    if (active) {
+      for (int base = rl; base < crow; base += rpb * UNROLL) {
+        uint32_t r[UNROLL];
+        uint32_t word[UNROLL];
+        int2 gp[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+          int i = base + u * rpb;
+          bool ok = i < crow;
+          int pos = pos0 + c0 + (ok ? i : 0);
+          r[u] = identity ? (uint32_t)pos : __ldg(row_idx + pos);
+          word[u] = 0xFFFFFFFFu;
+          if (ok) word[u] = __ldg(bins32 + (size_t)r[u] * wpr + w);
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) gp[u] = __ldg(gpair + r[u]);
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint32_t b = (word[u] >> (8 * j)) & 255u;
+            if (b != CB_MISSING_BIN) {
+              atomicAdd(sG + off[j] + b, gp[u].x);
+              atomicAdd(sH + off[j] + b, gp[u].y);
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();
+    int32_t* pg = partials + (size_t)pid * 2 * S + tile.s0;
+    int32_t* ph = pg + S;
+    for (int s = threadIdx.x; s < St; s += blockDim.x) {
+      pg[s] = sG[s]; ph[s] = sH[s];
+      sG[s] = 0; sH[s] = 0;
+    }
+    __syncthreads();
+  }
+}
+
+// level buffer [slot][S][2] int64  <-  sum of the slot's int32 partials ([2][S] each)
+__global__ void __launch_bounds__(256) hist_reduce_kernel(const int32_t* __restrict__ partials,
+                                                          const HistPlan* __restrict__ plan, int S,
+                                                          int64_t* __restrict__ level_buf) {
+  const int j = blockIdx.y;
+  if (j >= plan->n_build) return;
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= S) return;
+  int64_t g = 0, h = 0;
+  const int p0 = plan->b_pbeg[j], p1 = plan->b_pbeg[j + 1];
+  const int32_t* pp = partials + (size_t)p0 * 2 * S + s;
+  for (int p = p0; p < p1; ++p, pp += 2 * (size_t)S) {
+    g += __ldg(pp);
+    h += __ldg(pp + S);
+  }
+  reinterpret_cast<longlong2*>(level_buf)[(size_t)j * S + s] = make_longlong2(g, h);
+}
+
+__global__ void subtract_kernel(const int64_t* __restrict__ a, const int64_t* __restrict__ b, int64_t* __restrict__ c,
+                                int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) c[i] = a[i] - b[i];
+}
+
+// =====================================================================================
+// K5  split scan: one warp per (node, feature); 8 bins per lane; exact int64 prefix sums;
+//     gains in f64 with one rounding per operation (bit-equal to the oracle)
+// =====================================================================================
+struct FeatBest {
+  float chg;      // 0 when the feature has no candidate
+  int split_bin;
+  int default_left;
+  int pad;
+  int64_t GL, HL;
+};
+
+__device__ __forceinline__ float split_chg(int64_t gl, int64_t hl, int64_t gr, int64_t hr, double ig, double ih,
+                                           float root_gain, const cb_tree_params& p) {
+  double HL = __dmul_rn((double)hl, ih), HR = __dmul_rn((double)hr, ih);
+  if (!(HL >= (double)p.min_child_weight && HR >= (double)p.min_child_weight)) return -1.0f;
+  double gain = __dadd_rn(calc_gain(__dmul_rn((double)gl, ig), HL, p), calc_gain(__dmul_rn((double)gr, ig), HR, p));
+  float chg = __double2float_rn(__dsub_rn(gain, (double)root_gain));
+  return isinf(chg) ? -1.0f : chg;
+}
+
+// returns the feature's best candidate to every lane
+__device__ __forceinline__ FeatBest scan_feature(const int64_t* __restrict__ hist, int nb, int64_t Gt, int64_t Ht,
+                                                 const cb_tree_params& p) {
+  const int lane = threadIdx.x & 31;
+  const double ig = ldexp(1.0, -p.sg), ih = ldexp(1.0, -p.sh);
+  const float root_gain = __double2float_rn(calc_gain(__dmul_rn((double)Gt, ig), __dmul_rn((double)Ht, ih), p));
+  int64_t g[8], h[8];
+  int64_t sg = 0, sh = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    int i = lane * 8 + k;
+    longlong2 v = i < nb ? __ldg(reinterpret_cast<const longlong2*>(hist) + i) : make_longlong2(0, 0);
+    sg += v.x; sh += v.y;
+    g[k] = sg; h[k] = sh;                     // inclusive prefix inside the lane
+  }
+  int64_t ig_ = sg, ih_ = sh;                 // warp inclusive scan of lane totals
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int64_t a = __shfl_up_sync(0xffffffffu, ig_, o), b = __shfl_up_sync(0xffffffffu, ih_, o);
+    if (lane >= o) { ig_ += a; ih_ += b; }
+  }
+  const int64_t exg = ig_ - sg, exh = ih_ - sh;   // sum of the lanes below
+  const int64_t Gf = __shfl_sync(0xffffffffu, ig_, 31), Hf = __shfl_sync(0xffffffffu, ih_, 31);
+  // forward: missing -> right; candidate i has left = prefix_incl(i)
+  float bc = 0.0f; int bi = -1;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    int i = lane * 8 + k;
+    if (i < nb) {
+      int64_t gl = exg + g[k], hl = exh + h[k];
+      float c = split_chg(gl, hl, Gt - gl, Ht - hl, ig, ih, root_gain, p);
+      if (c > bc) { bc = c; bi = i; }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {          // max chg, ties -> lower bin
+    float oc = __shfl_xor_sync(0xffffffffu, bc, o);
+    int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (oc > bc || (oc == bc && oi >= 0 && (bi < 0 || oi < bi))) { bc = oc; bi = oi; }
+  }
+  float best_c = bc; int best_bin = bi, best_dl = 0;
+  if (Gf != Gt || Hf != Ht) {
+    // backward: missing -> left; candidate i has right = sum of bins >= i; scan order is i descending
+    float cc = 0.0f; int ci = -1;
+#pragma unroll
+    for (int k = 7; k >= 0; --k) {
+      int i = lane * 8 + k;
+      if (i < nb) {
+        int64_t pg = exg + (k ? g[k - 1] : 0), ph = exh + (k ? h[k - 1] : 0);   // prefix_excl(i)
+        int64_t gr = Gf - pg, hr = Hf - ph;
+        float c = split_chg(Gt - gr, Ht - hr, gr, hr, ig, ih, root_gain, p);
+        if (c > cc) { cc = c; ci = i; }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {        // max chg, ties -> higher bin (earlier in scan order)
+      float oc = __shfl_xor_sync(0xffffffffu, cc, o);
+      int oi = __shfl_xor_sync(0xffffffffu, ci, o);
+      if (oc > cc || (oc == cc && oi > ci)) { cc = oc; ci = oi; }
+    }
+    if (cc > best_c) { best_c = cc; best_bin = ci - 1; best_dl = 1; }
+  }
+  FeatBest out;
+  out.chg = best_c; out.split_bin = best_bin; out.default_left = best_dl; out.pad = 0; out.GL = 0; out.HL = 0;
+  if (best_c > 0.0f) {
+    // left sums of the winning candidate: prefix_incl(best_bin) (+ missing when default_left)
+    int src = best_bin >= 0 ? best_bin >> 3 : 0;
+    int64_t gl = 0, hl = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (lane * 8 + k == best_bin) { gl = exg + g[k]; hl = exh + h[k]; }
+    gl = __shfl_sync(0xffffffffu, gl, src); hl = __shfl_sync(0xffffffffu, hl, src);
+    if (best_bin < 0) { gl = 0; hl = 0; }
+    if (best_dl) { gl += Gt - Gf; hl += Ht - Hf; }
+    out.GL = gl; out.HL = hl;
+  }
+  return out;
+}
+
+// =====================================================================================
+// K6  stable partition, standalone single-segment form (the trainer has the level-wide form)
+// =====================================================================================
+__device__ __forceinline__ bool goes_left(const uint8_t* __restrict__ bins, int64_t ldb, uint32_t row, int feat,
+                                          int split_bin, int default_left) {
+  int c = __ldg(bins + (size_t)row * ldb + feat);
+  return c == CB_MISSING_BIN ? default_left != 0 : c <= split_bin;
+}
+
+__global__ void __launch_bounds__(256) part1_flags_kernel(const uint8_t* __restrict__ bins, int64_t ldb,
+                                                          const uint32_t* __restrict__ seg, int64_t count, int feat,
+                                                          int split_bin, int default_left,
+                                                          uint32_t* __restrict__ flag_bits, int* __restrict__ tile_cnt) {
+  __shared__ int wsum[8];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int64_t tile0 = (int64_t)blockIdx.x * kPartTile;
+  int cnt = 0;
+  for (int it = 0; it < kPartTile / 256; ++it) {
+    int64_t pos = tile0 + (int64_t)wid * (kPartTile / 8) + it * 32 + lane;
+    bool fl = false;
+    if (pos < count) fl = goes_left(bins, ldb, seg[pos], feat, split_bin, default_left);
+    uint32_t bal = __ballot_sync(0xffffffffu, fl);
+    if (lane == 0 && pos < count) flag_bits[pos >> 5] = bal;
+    cnt += __popc(bal);
+  }
+  if (lane == 0) wsum[wid] = cnt;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int k = 0; k < 8; ++k) t += wsum[k];
+    tile_cnt[blockIdx.x] = t;
+  }
+}
+
+// one block: exclusive scan of tile counts in place; total -> *n_left
+__global__ void __launch_bounds__(1024) part2_scan_kernel(int* __restrict__ tile_cnt, int n_tiles,
+                                                          int64_t* __restrict__ n_left) {
+  __shared__ int part[1024];
+  const int per = (n_tiles + 1023) / 1024;
+  const int b = threadIdx.x * per, e = min(n_tiles, b + per);
+  int s = 0;
+  for (int i = b; i < e; ++i) s += tile_cnt[i];
+  part[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 1; o < 1024; o <<= 1) {
+    int v = threadIdx.x >= o ? part[threadIdx.x - o] : 0;
+    __syncthreads();
+    part[threadIdx.x] += v;
+    __syncthreads();
+  }
+  int run = part[threadIdx.x] - s;
+  for (int i = b; i < e; ++i) { int c = tile_cnt[i]; tile_cnt[i] = run; run += c; }
+  if (threadIdx.x == 1023 && n_left) *n_left = part[1023];
+}
+
+__global__ void __launch_bounds__(256) part3_scatter_kernel(const uint32_t* __restrict__ seg, int64_t count,
+                                                            const uint32_t* __restrict__ flag_bits,
+                                                            const int* __restrict__ tile_ex,
+                                                            const int64_t* __restrict__ n_left,
+                                                            uint32_t* __restrict__ out) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int64_t tile0 = (int64_t)blockIdx.x * kPartTile;
+  const int64_t w0 = tile0 >> 5;                 // first flag word of the tile
+  const int wpw = kPartTile / 8 / 32;            // flag words per warp (8)
+  // lefts in this tile before this warp's first position
+  int before = 0;
+  for (int k = lane; k < wid * wpw; k += 32) {
+    int64_t wi = w0 + k;
+    if (wi * 32 < count) before += __popc(flag_bits[wi]);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) before += __shfl_xor_sync(0xffffffffu, before, o);
+  int64_t run = (int64_t)tile_ex[blockIdx.x] + before;
+  const int64_t nl = *n_left;
+  for (int it = 0; it < wpw; ++it) {
+    int64_t pos = tile0 + (int64_t)wid * (kPartTile / 8) + it * 32 + lane;
+    if (pos - lane >= count) break;
+    uint32_t bal = flag_bits[pos >> 5];
+    if (pos < count) {
+      bool fl = (bal >> lane) & 1u;
+      int64_t lbefore = run + __popc(bal & ((1u << lane) - 1u));
+      int64_t dest = fl ? lbefore : nl + (pos - lbefore);
+      out[dest] = seg[pos];
+    }
+    run += __popc(bal);
+  }
+}
+
+// =====================================================================================
+// K8  ensemble traversal: 256 rows per CTA staged feature-major in shared memory
+//     (address = f * 256 + row -> bank = lane: conflict free whatever the feature)
+// =====================================================================================
+constexpr int kPredRows = 256;
+
+__global__ void __launch_bounds__(kPredRows) predict_kernel(const float* __restrict__ X, int64_t n, int f, int64_t ldx,
+                                                            const uint2* __restrict__ nodes,
+                                                            const int32_t* __restrict__ tree_off, int n_trees,
+                                                            float base_margin, float* __restrict__ out_margin,
+                                                            float* __restrict__ out_proba) {
+  extern __shared__ float xs[];   // [f][kPredRows]
+  const int64_t row0 = (int64_t)blockIdx.x * kPredRows;
+  const int nrow = (int)min((int64_t)kPredRows, n - row0);
+  if (ldx == f) {                 // contiguous tile: coalesced read, transposing store
+    const float* src = X + row0 * ldx;
+    for (int i = threadIdx.x; i < nrow * f; i += kPredRows) {
+      int r = i / f, c = i - r * f;
+      xs[c * kPredRows + r] = __ldg(src + i);
+    }
+  } else {
+    for (int i = threadIdx.x; i < nrow * f; i += kPredRows) {
+      int r = i / f, c = i - r * f;
+      xs[c * kPredRows + r] = __ldg(X + (row0 + r) * ldx + c);
+    }
+  }
+  __syncthreads();
+  const int r = threadIdx.x;
+  if (r >= nrow) return;
+  float m = base_margin;
+  for (int t = 0; t < n_trees; ++t) {
+    const uint2* tn = nodes + __ldg(tree_off + t);
+    uint2 nd = __ldg(tn);
+    while (nd.y >> 16) {
+      float v = xs[(nd.y & 0x7FFFu) * kPredRows + r];
+      bool left = (v != v) ? ((nd.y >> 15) & 1u) : (v < __uint_as_float(nd.x));
+      nd = __ldg(tn + (nd.y >> 16) + (left ? 0u : 1u));
+    }
+    m = __fadd_rn(m, __uint_as_float(nd.x));
+  }
+  if (out_margin) out_margin[row0 + r] = m;
+  if (out_proba) out_proba[row0 + r] = spec_sigmoid(m);
+}
+
+}  // namespace cb

@@ -1,0 +1,380 @@
+// Level-wise tree growth with every decision on the device.  Included by cobalt_gbdt.cu only.
+#pragma once
+#include "kernels.cuh"
+
+namespace cb {
+
+constexpr int kMaxDepth = 9;              // levels 0..8 are split; level nodes <= 256
+constexpr int kMaxLevelNodes = 256;
+
+struct TreeState {                        // device memory
+  int n_nodes;
+  int lvl_first[kMaxDepth + 2];
+  int lvl_count[kMaxDepth + 2];
+  int pad_;
+  long long root_tot[2];                  // local sum of (q_g, q_h), filled by the gradient kernel
+};
+
+// the level's nodes in id order (= ascending position order): what the partition pass needs
+struct LevelSegs {
+  int n;
+  int begin[kMaxLevelNodes], count[kMaxLevelNodes];
+  int kind[kMaxLevelNodes];               // 0 leaf now, 1 split + partition, 2 split, children are leaves
+  int feat[kMaxLevelNodes], bin[kMaxLevelNodes], dl[kMaxLevelNodes], child[kMaxLevelNodes];
+  float leafL[kMaxLevelNodes], leafR[kMaxLevelNodes];
+  int Lb[kMaxLevelNodes], nleft[kMaxLevelNodes];
+};
+
+struct NodeArrays {                       // device arrays [max_nodes]
+  int* begin; int* count; long long* G; long long* H;
+};
+
+struct TreeOut {                          // slices of the forest arrays for the tree being grown
+  int32_t* left; int32_t* right; int32_t* parent; int32_t* split_index; int32_t* split_bin;
+  float* split_cond; uint8_t* default_left; float* base_weight; float* loss_chg; float* sum_hess;
+};
+
+__global__ void round_init_kernel(TreeState* st, NodeArrays na, TreeOut to, int max_nodes, int n_rows,
+                                  HistPlan* plan, int grid) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < max_nodes) {
+    to.left[i] = -1; to.right[i] = -1; to.parent[i] = 2147483647; to.split_index[i] = 0; to.split_bin[i] = 0;
+    to.split_cond[i] = 0.0f; to.default_left[i] = 0; to.base_weight[i] = 0.0f; to.loss_chg[i] = 0.0f;
+    to.sum_hess[i] = 0.0f;
+  }
+  if (i == 0) {
+    st->n_nodes = 1;
+    for (int l = 0; l < kMaxDepth + 2; ++l) { st->lvl_first[l] = 0; st->lvl_count[l] = 0; }
+    st->lvl_first[0] = 0; st->lvl_count[0] = 1;
+    na.begin[0] = 0; na.count[0] = n_rows;
+    int b0 = 0, c0 = n_rows;
+    plan->b_node[0] = 0; plan->b_sibling[0] = -1; plan->b_parent[0] = -1;
+    plan_ctas(plan, 1, &b0, &c0, grid);
+  }
+}
+
+// level buffer tail (level 0 only): the local root totals, summed over ranks with the histogram
+__global__ void root_totals_kernel(const TreeState* st, int64_t* level_buf_tail) {
+  level_buf_tail[0] = st->root_tot[0];
+  level_buf_tail[1] = st->root_tot[1];
+}
+
+// pool[node] = built; pool[sibling] = pool[parent] - built   (K9, exact)
+__global__ void __launch_bounds__(256) hist_finalize_kernel(const int64_t* __restrict__ level_buf,
+                                                            const HistPlan* __restrict__ plan, int S2,
+                                                            int64_t* __restrict__ pool, NodeArrays na,
+                                                            const int64_t* tail) {
+  const int j = blockIdx.y;
+  if (j >= plan->n_build) return;
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (tail && j == 0 && v == 0) { na.G[0] = tail[0]; na.H[0] = tail[1]; }
+  if (v >= S2) return;
+  const int64_t built = level_buf[(size_t)j * S2 + v];
+  pool[(size_t)plan->b_node[j] * S2 + v] = built;
+  const int sib = plan->b_sibling[j];
+  if (sib >= 0) pool[(size_t)sib * S2 + v] = pool[(size_t)plan->b_parent[j] * S2 + v] - built;
+}
+
+__global__ void __launch_bounds__(128) scan_level_kernel(const int64_t* __restrict__ pool,
+                                                         const int32_t* __restrict__ bin_ptr, int f, int S2,
+                                                         const TreeState* __restrict__ st, int level, NodeArrays na,
+                                                         cb_tree_params p, const uint8_t* __restrict__ feature_mask,
+                                                         FeatBest* __restrict__ feat_best) {
+  const int i = blockIdx.y;
+  if (i >= st->lvl_count[level]) return;
+  const int feat = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (feat >= f) return;
+  const int nid = st->lvl_first[level] + i;
+  FeatBest fb;
+  fb.chg = 0.0f; fb.split_bin = -1; fb.default_left = 0; fb.pad = 0; fb.GL = 0; fb.HL = 0;
+  if (!feature_mask || feature_mask[feat]) {
+    const int b0 = __ldg(bin_ptr + feat), nb = __ldg(bin_ptr + feat + 1) - b0;
+    fb = scan_feature(pool + (size_t)nid * S2 + 2 * (size_t)b0, nb, na.G[nid], na.H[nid], p);
+  }
+  if ((threadIdx.x & 31) == 0) feat_best[(size_t)i * f + feat] = fb;
+}
+
+// one block: pick each node's best feature, allocate children in node-id order (R9),
+// write the tree arrays, the children's totals and the level's segment table
+__global__ void __launch_bounds__(256) level_finish_kernel(TreeState* st, int level, int max_depth,
+                                                           const FeatBest* __restrict__ feat_best, int f,
+                                                           const float* __restrict__ cuts,
+                                                           const float* __restrict__ min_vals, cb_tree_params p,
+                                                           NodeArrays na, TreeOut to, LevelSegs* segs) {
+  __shared__ float s_chg[kMaxLevelNodes];
+  __shared__ int s_feat[kMaxLevelNodes];
+  __shared__ int s_child[kMaxLevelNodes];
+  const int first = st->lvl_first[level], cnt = st->lvl_count[level];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const double ig = ldexp(1.0, -p.sg), ih = ldexp(1.0, -p.sh);
+  for (int i = wid; i < cnt; i += 8) {
+    float bc = 0.0f; int bf = -1;
+    for (int j = lane; j < f; j += 32) {
+      float c = feat_best[(size_t)i * f + j].chg;
+      if (c > bc) { bc = c; bf = j; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {      // max chg, ties -> lower feature index
+      float oc = __shfl_xor_sync(0xffffffffu, bc, o);
+      int of = __shfl_xor_sync(0xffffffffu, bf, o);
+      if (oc > bc || (oc == bc && of >= 0 && (bf < 0 || of < bf))) { bc = oc; bf = of; }
+    }
+    if (lane == 0) { s_chg[i] = bc; s_feat[i] = bf; }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (level == 0) {
+      to.base_weight[0] = __double2float_rn(calc_weight(__dmul_rn((double)na.G[0], ig), __dmul_rn((double)na.H[0], ih), p));
+      to.sum_hess[0] = __double2float_rn(__dmul_rn((double)na.H[0], ih));
+    }
+    int next = st->n_nodes;
+    const int old = next;
+    for (int i = 0; i < cnt; ++i) {
+      const int nid = first + i, bf = s_feat[i];
+      bool valid = false;
+      if (bf >= 0) {
+        const FeatBest fb = feat_best[(size_t)i * f + bf];
+        const long long HL = fb.HL, HR = na.H[nid] - fb.HL;
+        valid = s_chg[i] > 1e-6f && !(s_chg[i] < p.gamma) && level < max_depth && HL != 0 && HR != 0;
+      }
+      if (valid) { s_child[i] = next; next += 2; } else s_child[i] = -1;
+    }
+    st->n_nodes = next;
+    st->lvl_first[level + 1] = old;
+    st->lvl_count[level + 1] = next - old;
+    segs->n = cnt;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+    const int nid = first + i;
+    segs->begin[i] = na.begin[nid];
+    segs->count[i] = na.count[nid];
+    segs->Lb[i] = 0; segs->nleft[i] = 0;
+    const int L = s_child[i];
+    if (L < 0) {
+      const float leaf = __fmul_rn(to.base_weight[nid], p.eta);
+      to.split_cond[nid] = leaf;
+      to.base_weight[nid] = leaf;
+      segs->kind[i] = 0; segs->leafL[i] = leaf; segs->leafR[i] = leaf;
+      segs->feat[i] = 0; segs->bin[i] = 0; segs->dl[i] = 0; segs->child[i] = -1;
+      continue;
+    }
+    const int R = L + 1, bf = s_feat[i];
+    const FeatBest fb = feat_best[(size_t)i * f + bf];
+    const long long GL = fb.GL, HL = fb.HL, GR = na.G[nid] - GL, HR = na.H[nid] - HL;
+    to.left[nid] = L; to.right[nid] = R; to.parent[L] = nid; to.parent[R] = nid;
+    to.split_index[nid] = bf; to.split_bin[nid] = fb.split_bin;
+    to.split_cond[nid] = fb.split_bin >= 0 ? cuts[(size_t)bf * CB_CUT_STRIDE + fb.split_bin] : min_vals[bf];
+    to.default_left[nid] = (uint8_t)fb.default_left;
+    to.loss_chg[nid] = s_chg[i];
+    na.G[L] = GL; na.H[L] = HL; na.G[R] = GR; na.H[R] = HR;
+    const float bwL = __double2float_rn(calc_weight(__dmul_rn((double)GL, ig), __dmul_rn((double)HL, ih), p));
+    const float bwR = __double2float_rn(calc_weight(__dmul_rn((double)GR, ig), __dmul_rn((double)HR, ih), p));
+    to.sum_hess[L] = __double2float_rn(__dmul_rn((double)HL, ih));
+    to.sum_hess[R] = __double2float_rn(__dmul_rn((double)HR, ih));
+    segs->feat[i] = bf; segs->bin[i] = fb.split_bin; segs->dl[i] = fb.default_left; segs->child[i] = L;
+    if (level + 1 == max_depth) {
+      const float lL = __fmul_rn(bwL, p.eta), lR = __fmul_rn(bwR, p.eta);
+      to.split_cond[L] = lL; to.base_weight[L] = lL;
+      to.split_cond[R] = lR; to.base_weight[R] = lR;
+      segs->kind[i] = 2; segs->leafL[i] = lL; segs->leafR[i] = lR;
+    } else {
+      to.base_weight[L] = bwL; to.base_weight[R] = bwR;
+      segs->kind[i] = 1; segs->leafL[i] = 0.0f; segs->leafR[i] = 0.0f;
+    }
+  }
+}
+
+// segment of a position: largest i with begin[i] <= pos, valid when pos < begin[i] + count[i]
+__device__ __forceinline__ int find_seg(const int* __restrict__ s_begin, const int* __restrict__ s_count, int n,
+                                        int pos) {
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (s_begin[mid] <= pos) lo = mid + 1; else hi = mid;
+  }
+  int i = lo - 1;
+  if (i < 0 || pos >= s_begin[i] + s_count[i]) return -1;
+  return i;
+}
+
+struct SegCache {
+  int begin[kMaxLevelNodes], count[kMaxLevelNodes];
+};
+
+// P1: go-left flags of every position that sits in a node being split (kind 1)
+__global__ void __launch_bounds__(256) part_level_flags_kernel(const uint8_t* __restrict__ bins, int64_t ldb,
+                                                               const uint32_t* __restrict__ rows_in, int identity,
+                                                               int n_rows, const LevelSegs* __restrict__ segs,
+                                                               uint32_t* __restrict__ flag_bits,
+                                                               int* __restrict__ tile_cnt) {
+  __shared__ SegCache sc;
+  __shared__ int wsum[8];
+  const int n = segs->n;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) { sc.begin[i] = segs->begin[i]; sc.count[i] = segs->count[i]; }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int tile0 = blockIdx.x * kPartTile;
+  int cnt = 0;
+  for (int it = 0; it < kPartTile / 256; ++it) {
+    const int pos = tile0 + wid * (kPartTile / 8) + it * 32 + lane;
+    bool fl = false;
+    if (pos < n_rows) {
+      const int i = find_seg(sc.begin, sc.count, n, pos);
+      if (i >= 0 && segs->kind[i] == 1) {
+        const uint32_t row = identity ? (uint32_t)pos : __ldg(rows_in + pos);
+        fl = goes_left(bins, ldb, row, segs->feat[i], segs->bin[i], segs->dl[i]);
+      }
+    }
+    const uint32_t bal = __ballot_sync(0xffffffffu, fl);
+    if (lane == 0 && pos < n_rows) flag_bits[pos >> 5] = bal;
+    cnt += __popc(bal);
+  }
+  if (lane == 0) wsum[wid] = cnt;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int k = 0; k < 8; ++k) t += wsum[k];
+    tile_cnt[blockIdx.x] = t;
+  }
+}
+
+// number of lefts strictly before position p (global prefix over all positions)
+__device__ __forceinline__ int lefts_before(const int* __restrict__ tile_ex, const uint32_t* __restrict__ flag_bits,
+                                            int p, int n_rows) {
+  if (p <= 0) return 0;
+  const int tile = p / kPartTile;
+  if (tile * kPartTile >= n_rows) {       // p == n_rows on a tile boundary: everything before
+    int t = tile - 1;
+    int s = tile_ex[t];
+    for (int w = t * (kPartTile / 32); w * 32 < n_rows; ++w) s += __popc(flag_bits[w]);
+    return s;
+  }
+  int s = tile_ex[tile];
+  const int w0 = tile * (kPartTile / 32), w1 = p >> 5;
+  for (int w = w0; w < w1; ++w) s += __popc(flag_bits[w]);
+  if ((p & 31) && w1 * 32 < n_rows) s += __popc(flag_bits[w1] & ((1u << (p & 31)) - 1u));
+  return s;
+}
+
+// P2 (one block): scan tile counts, place the children segments, plan the next level's histograms
+__global__ void __launch_bounds__(1024) part_level_scan_kernel(int* __restrict__ tile_cnt, int n_tiles, int n_rows,
+                                                               const uint32_t* __restrict__ flag_bits,
+                                                               LevelSegs* segs, TreeState* st, int level,
+                                                               int max_depth, NodeArrays na, HistPlan* plan, int grid,
+                                                               int by_hessian) {
+  __shared__ int part[1024];
+  __shared__ int b_begin[kMaxBuild], b_count[kMaxBuild];
+  const int per = (n_tiles + 1023) / 1024;
+  const int b = threadIdx.x * per, e = min(n_tiles, b + per);
+  int s = 0;
+  for (int i = b; i < e; ++i) s += tile_cnt[i];
+  part[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 1; o < 1024; o <<= 1) {
+    int v = threadIdx.x >= o ? part[threadIdx.x - o] : 0;
+    __syncthreads();
+    part[threadIdx.x] += v;
+    __syncthreads();
+  }
+  int run = part[threadIdx.x] - s;
+  for (int i = b; i < e; ++i) { int c = tile_cnt[i]; tile_cnt[i] = run; run += c; }
+  __threadfence_block();
+  __syncthreads();
+  const int n = segs->n;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    if (segs->kind[i] != 1) continue;
+    const int bg = segs->begin[i], ct = segs->count[i];
+    const int Lb = lefts_before(tile_cnt, flag_bits, bg, n_rows);
+    const int Le = lefts_before(tile_cnt, flag_bits, bg + ct, n_rows);
+    const int nl = Le - Lb;
+    segs->Lb[i] = Lb; segs->nleft[i] = nl;
+    const int L = segs->child[i];
+    na.begin[L] = bg; na.count[L] = nl;
+    na.begin[L + 1] = bg + nl; na.count[L + 1] = ct - nl;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int nb = 0;
+    if (level + 1 < max_depth) {
+      const int first = st->lvl_first[level];
+      for (int i = 0; i < n; ++i) {
+        if (segs->kind[i] != 1) continue;
+        const int L = segs->child[i], R = L + 1;
+        const bool left_small = by_hessian ? (na.H[L] <= na.H[R]) : (na.count[L] <= na.count[R]);
+        const int bn = left_small ? L : R;
+        plan->b_node[nb] = bn; plan->b_sibling[nb] = left_small ? R : L; plan->b_parent[nb] = first + i;
+        b_begin[nb] = na.begin[bn]; b_count[nb] = na.count[bn];
+        ++nb;
+      }
+    }
+    plan_ctas(plan, nb, b_begin, b_count, grid);
+  }
+}
+
+// P3: stable scatter of split nodes (lefts first), leaf values of nodes that stopped here
+__global__ void __launch_bounds__(256) part_level_scatter_kernel(const uint32_t* __restrict__ rows_in, int identity,
+                                                                 int n_rows, const LevelSegs* __restrict__ segs,
+                                                                 const uint32_t* __restrict__ flag_bits,
+                                                                 const int* __restrict__ tile_ex,
+                                                                 uint32_t* __restrict__ rows_out,
+                                                                 float* __restrict__ margin) {
+  __shared__ SegCache sc;
+  const int n = segs->n;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) { sc.begin[i] = segs->begin[i]; sc.count[i] = segs->count[i]; }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int tile0 = blockIdx.x * kPartTile;
+  const int w0 = tile0 >> 5, wpw = kPartTile / 8 / 32;
+  int before = 0;
+  for (int k = lane; k < wid * wpw; k += 32)
+    if ((w0 + k) * 32 < n_rows) before += __popc(flag_bits[w0 + k]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) before += __shfl_xor_sync(0xffffffffu, before, o);
+  int run = tile_ex[blockIdx.x] + before;
+  for (int it = 0; it < wpw; ++it) {
+    const int pos = tile0 + wid * (kPartTile / 8) + it * 32 + lane;
+    if (pos - lane >= n_rows) break;
+    const uint32_t bal = flag_bits[pos >> 5];
+    if (pos < n_rows) {
+      const uint32_t row = identity ? (uint32_t)pos : __ldg(rows_in + pos);
+      const int i = find_seg(sc.begin, sc.count, n, pos);
+      int dest = pos;
+      if (i >= 0) {
+        const int kind = segs->kind[i];
+        if (kind == 1) {
+          const int lb = run + __popc(bal & ((1u << lane) - 1u)) - segs->Lb[i];   // lefts before, inside the node
+          const int bg = sc.begin[i];
+          dest = ((bal >> lane) & 1u) ? bg + lb : bg + segs->nleft[i] + (pos - bg - lb);
+        } else if (kind == 0) {
+          margin[row] = __fadd_rn(margin[row], segs->leafL[i]);
+        }
+      }
+      rows_out[dest] = row;
+    }
+    run += __popc(bal);
+  }
+}
+
+// last level: children are leaves, so rows are not moved; each row takes its child's leaf value
+__global__ void __launch_bounds__(256) final_apply_kernel(const uint8_t* __restrict__ bins, int64_t ldb,
+                                                          const uint32_t* __restrict__ rows_in, int identity,
+                                                          int n_rows, const LevelSegs* __restrict__ segs,
+                                                          float* __restrict__ margin) {
+  __shared__ SegCache sc;
+  const int n = segs->n;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) { sc.begin[i] = segs->begin[i]; sc.count[i] = segs->count[i]; }
+  __syncthreads();
+  const int pos = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pos >= n_rows) return;
+  const int i = find_seg(sc.begin, sc.count, n, pos);
+  if (i < 0) return;
+  const uint32_t row = identity ? (uint32_t)pos : __ldg(rows_in + pos);
+  float leaf = segs->leafL[i];
+  if (segs->kind[i] == 2 && !goes_left(bins, ldb, row, segs->feat[i], segs->bin[i], segs->dl[i])) leaf = segs->leafR[i];
+  margin[row] = __fadd_rn(margin[row], leaf);
+}
+
+__global__ void round_end_kernel(const TreeState* st, int32_t* n_nodes_out) { *n_nodes_out = st->n_nodes; }
+
+}  // namespace cb

@@ -1,0 +1,175 @@
+"""Torch-tensor front end of the C ABI: device memory and streams come from torch, every
+computation is a call into libcobalt_gbdt.so.  All tensors must live on a CUDA device."""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+
+from . import _lib
+from ._lib import CB_CUT_STRIDE, CB_QBITS, Split, TreeParams, check
+
+
+def _stream() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t: torch.Tensor | None) -> C.c_void_p:
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _need_cuda(*ts: torch.Tensor) -> None:
+    if not torch.cuda.is_available():
+        raise _lib.CobaltError("no CUDA device: this package has no CPU path")
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.CobaltError("expected CUDA tensors")
+
+
+def padded_ldb(n_features: int) -> int:
+    """Row stride of the u8 bin matrix: multiple of 16 bytes (whole 32-byte sectors when possible)."""
+    return (n_features + 15) // 16 * 16
+
+
+def quant_shifts(wmax: float) -> tuple[int, int]:
+    """R4: wmax * 2^sg <= 2^CB_QBITS; hessians (<= wmax / 4) carry two more fractional bits."""
+    e = math.frexp(float(wmax))[1]
+    if float(wmax) == 2.0 ** (e - 1):
+        e -= 1
+    sg = CB_QBITS - e
+    return sg, sg + 2
+
+
+def keep_threshold(subsample: float) -> int:
+    return 0 if subsample >= 1.0 else int(math.floor(float(subsample) * 4294967296.0))
+
+
+def workspace(nbytes: int, device) -> torch.Tensor:
+    return torch.empty(max(int(nbytes), 256) + 256, dtype=torch.uint8, device=device)
+
+
+def _aligned(ws: torch.Tensor) -> tuple[C.c_void_p, int]:
+    p = ws.data_ptr()
+    a = (p + 255) & ~255
+    return C.c_void_p(a), ws.numel() - (a - p)
+
+
+def sketch_cuts(X: torch.Tensor, max_bin: int = 256):
+    """K1.  X: f32 [n, f] (row stride may exceed f).  Returns cuts [f,256], n_cuts [f], min_vals [f]."""
+    _need_cuda(X)
+    assert X.dtype == torch.float32 and X.dim() == 2 and X.stride(1) == 1
+    n, f = X.shape
+    lib = _lib.load()
+    need = C.c_size_t()
+    check(lib.cb_sketch_workspace_bytes(n, f, C.byref(need)))
+    ws = workspace(need.value, X.device)
+    cuts = torch.empty((f, CB_CUT_STRIDE), dtype=torch.float32, device=X.device)
+    n_cuts = torch.empty(f, dtype=torch.int32, device=X.device)
+    min_vals = torch.empty(f, dtype=torch.float32, device=X.device)
+    wp, wb = _aligned(ws)
+    check(lib.cb_sketch_cuts(_ptr(X), n, f, X.stride(0), max_bin, _ptr(cuts), _ptr(n_cuts), _ptr(min_vals), wp, wb,
+                             _stream()))
+    return cuts, n_cuts, min_vals
+
+
+def bin_ptr_of(n_cuts: torch.Tensor) -> torch.Tensor:
+    bp = torch.zeros(n_cuts.numel() + 1, dtype=torch.int32, device=n_cuts.device)
+    bp[1:] = torch.cumsum(n_cuts, 0)
+    return bp
+
+
+def bin_pack(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, ldb: int | None = None) -> torch.Tensor:
+    """K2.  Returns u8 [n, ldb]."""
+    _need_cuda(X, cuts, n_cuts)
+    assert X.dtype == torch.float32 and X.stride(1) == 1
+    n, f = X.shape
+    ldb = ldb or padded_ldb(f)
+    bins = torch.empty((n, ldb), dtype=torch.uint8, device=X.device)
+    check(_lib.load().cb_bin_pack_u8(_ptr(X), n, f, X.stride(0), _ptr(cuts), _ptr(n_cuts), _ptr(bins), ldb, _stream()))
+    return bins
+
+
+def sigmoid(margin: torch.Tensor) -> torch.Tensor:
+    _need_cuda(margin)
+    out = torch.empty_like(margin)
+    check(_lib.load().cb_sigmoid(_ptr(margin), margin.numel(), _ptr(out), _stream()))
+    return out
+
+
+def grad_logistic(margin, y, weight, spw, sg, sh, subsample=1.0, seed=0, tree=0, row_offset=0):
+    """K3.  Returns (gpair int32 [n,2], totals int64 [2])."""
+    _need_cuda(margin, y)
+    n = margin.numel()
+    gp = torch.empty((n, 2), dtype=torch.int32, device=margin.device)
+    tot = torch.zeros(2, dtype=torch.int64, device=margin.device)
+    check(_lib.load().cb_grad_logistic_q(_ptr(margin), _ptr(y), _ptr(weight), n, float(spw), sg, sh,
+                                         keep_threshold(subsample), seed, tree, row_offset, _ptr(gp), _ptr(tot),
+                                         _stream()))
+    return gp, tot
+
+
+def hist_build(bins, n_features, gpair, row_idx, bin_ptr, total_bins, count=None) -> torch.Tensor:
+    """K4.  Returns int64 [total_bins, 2]."""
+    _need_cuda(bins, gpair, bin_ptr)
+    lib = _lib.load()
+    cnt = int(count if count is not None else (bins.shape[0] if row_idx is None else row_idx.numel()))
+    need = C.c_size_t()
+    check(lib.cb_hist_workspace_bytes(cnt, total_bins, C.byref(need)))
+    ws = workspace(need.value, bins.device)
+    hist = torch.empty((total_bins, 2), dtype=torch.int64, device=bins.device)
+    wp, wb = _aligned(ws)
+    check(lib.cb_hist_build(_ptr(bins), bins.stride(0), n_features, _ptr(gpair), _ptr(row_idx), cnt, _ptr(bin_ptr),
+                            total_bins, _ptr(hist), wp, wb, _stream()))
+    return hist
+
+
+def hist_subtract(parent, built) -> torch.Tensor:
+    out = torch.empty_like(parent)
+    check(_lib.load().cb_hist_subtract(_ptr(parent), _ptr(built), _ptr(out), parent.numel(), _stream()))
+    return out
+
+
+def split_scan(hist, bin_ptr, cuts, min_vals, totals, tp: TreeParams, feature_mask=None) -> dict:
+    """K5 on one node.  Returns the split record as a dict (synchronises to read it)."""
+    _need_cuda(hist, bin_ptr, cuts, min_vals, totals)
+    lib = _lib.load()
+    f = bin_ptr.numel() - 1
+    need = C.c_size_t()
+    check(lib.cb_split_scan_workspace_bytes(f, C.byref(need)))
+    ws = workspace(need.value, hist.device)
+    out = torch.zeros(C.sizeof(Split), dtype=torch.uint8, device=hist.device)
+    wp, wb = _aligned(ws)
+    check(lib.cb_split_scan(_ptr(hist), _ptr(bin_ptr), f, _ptr(cuts), _ptr(min_vals), _ptr(totals), C.byref(tp),
+                            _ptr(feature_mask), _ptr(out), wp, wb, _stream()))
+    rec = Split.from_buffer_copy(out.cpu().numpy().tobytes())
+    return {k: getattr(rec, k) for k, _ in Split._fields_ if k != "pad_"}
+
+
+def partition_stable(bins, seg: torch.Tensor, feature: int, split_bin: int, default_left: int):
+    """K6 on one segment.  Returns (seg_out u32-as-int32 tensor, n_left)."""
+    _need_cuda(bins, seg)
+    lib = _lib.load()
+    cnt = seg.numel()
+    need = C.c_size_t()
+    check(lib.cb_partition_workspace_bytes(cnt, C.byref(need)))
+    ws = workspace(need.value, bins.device)
+    out = torch.empty_like(seg)
+    nl = torch.zeros(1, dtype=torch.int64, device=bins.device)
+    wp, wb = _aligned(ws)
+    check(lib.cb_partition_stable(_ptr(bins), bins.stride(0), _ptr(seg), cnt, feature, split_bin, default_left,
+                                  _ptr(out), _ptr(nl), wp, wb, _stream()))
+    return out, int(nl.item())
+
+
+def predict(X: torch.Tensor, nodes: torch.Tensor, tree_off: torch.Tensor, base_margin: float,
+            want_margin: bool = False, want_proba: bool = True):
+    """K8.  nodes: packed int64 [n_nodes]; tree_off: int32 [n_trees+1]."""
+    _need_cuda(X, nodes, tree_off)
+    assert X.dtype == torch.float32 and X.stride(1) == 1
+    n, f = X.shape
+    m = torch.empty(n, dtype=torch.float32, device=X.device) if want_margin else None
+    p = torch.empty(n, dtype=torch.float32, device=X.device) if want_proba else None
+    check(_lib.load().cb_predict(_ptr(X), n, f, X.stride(0), _ptr(nodes), _ptr(tree_off), tree_off.numel() - 1,
+                                 float(base_margin), _ptr(m), _ptr(p), _stream()))
+    return m, p

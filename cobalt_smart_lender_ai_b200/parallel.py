@@ -1,0 +1,81 @@
+"""Row-sharded data parallelism: the host-side glue around the one collective of the path.
+
+Rows are split contiguously over ranks (one process per GPU).  Replicated: cuts, parameters,
+the tree being grown.  Exchanged: label statistics (4 scalars, once), the key columns for
+the exact quantile sketch (once), and per tree level the int64 histogram buffer
+(``GpuTrainer.boost_one``).  Integer sums make every exchange order independent, so split
+decisions are bit-identical for any world size."""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+
+
+def _dist():
+    d = torch.distributed
+    return d if d.is_available() and d.is_initialized() and d.get_world_size() > 1 else None
+
+
+def shard_rows(n_total: int, rank: int, world: int) -> tuple[int, int]:
+    """Contiguous shard [begin, end) of rank; the first n_total % world ranks get one extra row."""
+    base, rem = divmod(n_total, world)
+    begin = rank * base + min(rank, rem)
+    return begin, begin + base + (1 if rank < rem else 0)
+
+
+def feature_slices(n_features: int, world: int) -> list[tuple[int, int]]:
+    return [shard_rows(n_features, r, world) for r in range(world)]
+
+
+def global_stats(pos_w: float, neg_w: float, wmax: float, n_local: int, device=None):
+    """Sums the weighted label counts over ranks, takes the max weight, and returns this rank's
+    global row offset.  Works on any backend (gloo on CPU tensors, nccl on CUDA tensors)."""
+    d = _dist()
+    if d is None:
+        return pos_w, neg_w, wmax, 0
+    dev = device if device is not None else "cpu"
+    s = torch.tensor([pos_w, neg_w], dtype=torch.float64, device=dev)
+    d.all_reduce(s)
+    m = torch.tensor([wmax], dtype=torch.float64, device=dev)
+    d.all_reduce(m, op=d.ReduceOp.MAX)
+    counts = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(d.get_world_size())]
+    d.all_gather(counts, torch.tensor([n_local], dtype=torch.int64, device=dev))
+    offset = int(sum(int(c.item()) for c in counts[: d.get_rank()]))
+    return float(s[0].item()), float(s[1].item()), float(m[0].item()), offset
+
+
+def sketch_cuts_global(Xd: torch.Tensor, max_bin: int):
+    """Exact R1 cuts over ALL ranks' rows, identical on every rank: rows are all-gathered, each
+    rank sorts its slice of the feature columns (K1), and the cut arrays are all-gathered."""
+    d = _dist()
+    if d is None:
+        return ops.sketch_cuts(Xd, max_bin)
+    world, rank = d.get_world_size(), d.get_rank()
+    n_loc = torch.tensor([Xd.shape[0]], dtype=torch.int64, device=Xd.device)
+    ns = [torch.zeros_like(n_loc) for _ in range(world)]
+    d.all_gather(ns, n_loc)
+    ns = [int(t.item()) for t in ns]
+    f = Xd.shape[1]
+    parts = [torch.empty((k, f), dtype=torch.float32, device=Xd.device) for k in ns]
+    d.all_gather(parts, Xd.contiguous())
+    full = torch.cat(parts, 0)
+    del parts
+    sl = feature_slices(f, world)
+    f0, f1 = sl[rank]
+    cuts = torch.full((f, 256), float("inf"), dtype=torch.float32, device=Xd.device)
+    n_cuts = torch.zeros(f, dtype=torch.int32, device=Xd.device)
+    min_vals = torch.zeros(f, dtype=torch.float32, device=Xd.device)
+    if f1 > f0:
+        c, k, m = ops.sketch_cuts(full[:, f0:f1], max_bin)
+        cuts[f0:f1], n_cuts[f0:f1], min_vals[f0:f1] = c, k, m
+    del full
+    # every rank owns a disjoint feature slice; a SUM/MAX over zero-initialised slices assembles the whole
+    cuts_bits = torch.where(torch.arange(f, device=Xd.device)[:, None].ge(f0) & torch.arange(f, device=Xd.device)[:, None].lt(f1),
+                            cuts.view(torch.int32), torch.zeros_like(cuts.view(torch.int32)))
+    d.all_reduce(cuts_bits)
+    d.all_reduce(n_cuts)
+    mv_bits = torch.where((torch.arange(f, device=Xd.device) >= f0) & (torch.arange(f, device=Xd.device) < f1),
+                          min_vals.view(torch.int32), torch.zeros(f, dtype=torch.int32, device=Xd.device))
+    d.all_reduce(mv_bits)
+    return cuts_bits.view(torch.float32), n_cuts, mv_bits.view(torch.float32)

@@ -1,0 +1,139 @@
+"""Boosting driver: owns the device buffers of one fit and steps the fused C-ABI trainer.
+
+Replaces the body of ``XGBClassifier.fit`` (reference call sites
+src/model_train_test/model_tree_train_test.py:118,159).  Python only sequences calls; all
+arithmetic, split decisions and row movement happen in libcobalt_gbdt.so on the device.
+With ``world_size > 1`` rows are sharded across ranks and the per-level histogram buffer is
+summed with ``torch.distributed.all_reduce`` (NCCL over NVLink) between the two halves of a
+level -- the path's one collective.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib, ops
+from ._lib import TrainBuffers, TrainConfig, TreeParams, check
+
+FOREST_FIELDS = (("left", torch.int32), ("right", torch.int32), ("parent", torch.int32),
+                 ("split_index", torch.int32), ("split_bin", torch.int32), ("split_cond", torch.float32),
+                 ("default_left", torch.uint8), ("base_weight", torch.float32), ("loss_chg", torch.float32),
+                 ("sum_hess", torch.float32))
+
+
+class GpuTrainer:
+    def __init__(self, bins: torch.Tensor, y: torch.Tensor, weight: torch.Tensor | None, n_features: int,
+                 bin_ptr: torch.Tensor, cuts: torch.Tensor, min_vals: torch.Tensor, *, max_depth: int = 6,
+                 eta: float = 0.3, reg_lambda: float = 1.0, reg_alpha: float = 0.0, gamma: float = 0.0,
+                 min_child_weight: float = 1.0, scale_pos_weight: float = 1.0, sg: int, sh: int,
+                 subsample: float = 1.0, seed: int = 0, max_trees: int = 100, base_margin: float = 0.0,
+                 row_offset: int = 0, group=None):
+        if not bins.is_cuda:
+            raise _lib.CobaltError("GpuTrainer needs CUDA tensors: this package has no CPU path")
+        self.lib = _lib.load()
+        self.dev = bins.device
+        self.group, self.world = None, 1
+        if group is not False and torch.distributed.is_available() and torch.distributed.is_initialized():
+            w = torch.distributed.get_world_size(group)
+            if w > 1:
+                self.world, self.group = w, group
+        n, ldb = bins.shape
+        total_bins = int(bin_ptr[-1].item())
+        self.n, self.f, self.max_depth, self.max_trees = n, n_features, max_depth, max_trees
+        self.max_nodes = (1 << (max_depth + 1)) - 1
+        self.bins, self.y, self.weight = bins, y.to(torch.uint8).contiguous(), weight
+        self.bin_ptr, self.cuts, self.min_vals = bin_ptr, cuts, min_vals
+        self.margin = torch.full((n,), float(base_margin), dtype=torch.float32, device=self.dev)
+        self.forest = {k: torch.zeros((max_trees, self.max_nodes), dtype=dt, device=self.dev) for k, dt in FOREST_FIELDS}
+        self.n_nodes = torch.zeros(max_trees, dtype=torch.int32, device=self.dev)
+        tp = TreeParams(float(np.float32(eta)), float(reg_lambda), float(reg_alpha), float(gamma),
+                        float(min_child_weight), int(max_depth), int(sg), int(sh))
+        self.cfg = TrainConfig(n, ldb, int(row_offset), n_features, total_bins, max_trees, self.world, tp,
+                               float(scale_pos_weight), ops.keep_threshold(subsample), int(seed) & 0xFFFFFFFF, 0)
+        need = C.c_size_t()
+        check(self.lib.cb_trainer_workspace_bytes(C.byref(self.cfg), C.byref(need)))
+        self.ws = ops.workspace(need.value, self.dev)
+        wp, wb = ops._aligned(self.ws)
+        self._ws_base = wp.value
+        p = lambda t: None if t is None else t.data_ptr()  # noqa: E731
+        self.buffers = TrainBuffers(p(self.bins), p(self.y), p(self.weight), p(self.margin), p(self.bin_ptr),
+                                    p(self.cuts), p(self.min_vals), *[p(self.forest[k]) for k, _ in FOREST_FIELDS],
+                                    p(self.n_nodes))
+        h = C.c_void_p()
+        check(self.lib.cb_trainer_create(C.byref(self.cfg), C.byref(self.buffers), wp, wb, C.byref(h)))
+        self.handle = h
+        self.n_trees = 0
+        self._level_views = {}
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.cb_trainer_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _level_view(self, level: int) -> torch.Tensor:
+        v = self._level_views.get(level)
+        if v is None:
+            ptr, nv = C.c_void_p(), C.c_int64()
+            check(self.lib.cb_trainer_level_buffer(self.handle, level, C.byref(ptr), C.byref(nv)))
+            off = ptr.value - self.ws.data_ptr()
+            v = self.ws[off: off + nv.value * 8].view(torch.int64)
+            self._level_views[level] = v
+        return v
+
+    def boost_one(self, feature_mask: torch.Tensor | None = None) -> None:
+        if self.n_trees >= self.max_trees:
+            raise _lib.CobaltError("forest capacity exhausted")
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        fm = None if feature_mask is None else C.c_void_p(feature_mask.data_ptr())
+        if self.world == 1:
+            check(self.lib.cb_trainer_boost_round(self.handle, self.n_trees, fm, st))
+        else:
+            check(self.lib.cb_trainer_round_begin(self.handle, self.n_trees, fm, st))
+            for level in range(self.max_depth):
+                check(self.lib.cb_trainer_level_hist(self.handle, level, st))
+                torch.distributed.all_reduce(self._level_view(level), group=self.group)
+                check(self.lib.cb_trainer_level_split(self.handle, level, st))
+            check(self.lib.cb_trainer_round_end(self.handle, st))
+        self.n_trees += 1
+
+    def boost(self, n_rounds: int, feature_masks: torch.Tensor | None = None) -> None:
+        for t in range(n_rounds):
+            self.boost_one(None if feature_masks is None else feature_masks[self.n_trees])
+
+    def launch_count(self) -> int:
+        return int(self.lib.cb_trainer_launch_count(self.handle))
+
+    def row_order(self) -> torch.Tensor | None:
+        ptr = C.c_void_p()
+        check(self.lib.cb_trainer_row_order(self.handle, C.byref(ptr)))
+        if not ptr.value:
+            return None
+        off = ptr.value - self.ws.data_ptr()
+        return self.ws[off: off + self.n * 4].view(torch.int32)
+
+    def node_hist(self, nid: int) -> torch.Tensor:
+        ptr = C.c_void_p()
+        check(self.lib.cb_trainer_node_hist(self.handle, nid, C.byref(ptr)))
+        off = ptr.value - self.ws.data_ptr()
+        s2 = 2 * self.cfg.total_bins
+        return self.ws[off: off + s2 * 8].view(torch.int64).view(-1, 2)
+
+    def forest_numpy(self) -> dict:
+        """Padded [T][max_nodes] device arrays -> flat wire-format arrays on the host."""
+        t = self.n_trees
+        nn = self.n_nodes[:t].cpu().numpy()
+        offs = np.zeros(t + 1, np.int64)
+        np.cumsum(nn, out=offs[1:])
+        out = {"tree_offsets": offs, "n_nodes": nn}
+        for k, _ in FOREST_FIELDS:
+            a = self.forest[k][:t].cpu().numpy()
+            out[k] = np.concatenate([a[i, :nn[i]] for i in range(t)]) if t else a.reshape(-1)
+        return out

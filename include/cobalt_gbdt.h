@@ -1,0 +1,184 @@
+/*
+ * cobalt_gbdt.h -- C ABI of libcobalt_gbdt.so, the sm_100a histogram-GBDT hot path.
+ *
+ * The reference has no FFI for this path: it calls the third-party xgboost package
+ * through its Python estimator.  Each entry point below therefore cites
+ * the reference call site whose work it takes over and the xgboost stage it replaces
+ * (K-numbers of SURVEY.md 2.1).  Callers: cobalt_smart_lender_ai_b200/_lib.py (ctypes);
+ * INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative cb_status otherwise; the message is
+ *     available from cb_last_error() (thread local); nothing throws across the boundary;
+ *   - all data pointers are DEVICE pointers owned by the caller unless a name says host;
+ *     the library never frees or reallocates caller memory;
+ *   - scratch memory is caller provided: ask the matching *_workspace_bytes() first;
+ *   - `stream` is a cudaStream_t passed as void*; work is enqueued, never synchronised,
+ *     unless the function name ends in _sync;
+ *   - integers are exact: gradients are fixed point (R4), histograms int64 (R5).
+ */
+#ifndef COBALT_GBDT_H_
+#define COBALT_GBDT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CB_VERSION 100
+#define CB_MISSING_BIN 255 /* u8 code of a missing value (R2) */
+#define CB_MAX_BINS 255    /* real bins per feature (R2) */
+#define CB_CUT_STRIDE 256  /* cuts are stored [n_features][256], padded with +inf */
+#define CB_QBITS 18        /* |q_g| <= 2^18 per row (R4); equals oracle.QBITS */
+
+typedef enum {
+  CB_OK = 0,
+  CB_ERR_INVALID = -1,   /* bad argument */
+  CB_ERR_WORKSPACE = -2, /* workspace too small */
+  CB_ERR_CUDA = -3,      /* a CUDA call failed; see cb_last_error() */
+  CB_ERR_UNSUPPORTED = -4
+} cb_status;
+
+int cb_version(void);
+const char* cb_last_error(void);
+/* SM count and opt-in shared memory per block of the current device. */
+int cb_device_info(int* sm_count, int* smem_optin_bytes);
+
+/* ---- K1 quantile sketch: per-feature cut arrays (R1).
+ * Replaces the implicit sketch inside XGBClassifier.fit
+ * (src/model_train_test/model_tree_train_test.py:118,159; max_bin 256 in the shipped model).
+ * X: f32 row major [n][ldx].  cuts: f32 [f][256]; n_cuts: i32 [f]; min_vals: f32 [f]. */
+int cb_sketch_workspace_bytes(int64_t n_rows, int n_features, size_t* bytes);
+int cb_sketch_cuts(const float* X, int64_t n_rows, int n_features, int64_t ldx, int max_bin, float* cuts,
+                   int32_t* n_cuts, float* min_vals, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- K2 bin-index packing (R2): bins u8 row major [n][ldb], ldb % 4 == 0, pad = 255.
+ * Replaces xgboost's GHistIndexMatrix build inside fit (same call sites as K1). */
+int cb_bin_pack_u8(const float* X, int64_t n_rows, int n_features, int64_t ldx, const float* cuts,
+                   const int32_t* n_cuts, uint8_t* bins, int64_t ldb, void* stream);
+
+/* ---- K3 logistic gradient/hessian in fixed point (R4).
+ * Replaces the binary:logistic objective with scale_pos_weight
+ * (src/model_train_test/model_tree_train_test.py:103-116).
+ * gpair: int32 [n][2].  totals: int64 [2], ADDED to (zero it first).  weight may be NULL.
+ * keep_thresh: 0 = keep every row, else a row is kept iff hash(seed, tree, row_offset+i) < keep_thresh. */
+int cb_grad_logistic_q(const float* margin, const uint8_t* y, const float* weight, int64_t n_rows, float spw,
+                       int sg, int sh, uint32_t keep_thresh, uint32_t seed, uint32_t tree, int64_t row_offset,
+                       int32_t* gpair, int64_t* totals, void* stream);
+/* p = sigmoid(margin) with the specified operation sequence (R4/R11). */
+int cb_sigmoid(const float* margin, int64_t n, float* out, void* stream);
+
+/* ---- K4 per-node histogram build (R5).  Replaces xgboost BuildHist inside fit.
+ * row_idx: u32 [count] or NULL (rows 0..count-1).  bin_ptr: i32 [f+1] (device).
+ * hist: int64 [total_bins][2], overwritten.  Missing rows are skipped. */
+int cb_hist_workspace_bytes(int64_t max_rows, int total_bins, size_t* bytes);
+int cb_hist_build(const uint8_t* bins, int64_t ldb, int n_features, const int32_t* gpair, const uint32_t* row_idx,
+                  int64_t count, const int32_t* bin_ptr, int total_bins, int64_t* hist, void* workspace,
+                  size_t workspace_bytes, void* stream);
+
+/* ---- K9 sibling = parent - built (exact). */
+int cb_hist_subtract(const int64_t* parent, const int64_t* built, int64_t* sibling, int64_t n_values, void* stream);
+
+/* ---- K5 split-gain scan (R6).  Replaces HistEvaluator::EnumerateSplit. */
+typedef struct {
+  float eta, reg_lambda, reg_alpha, gamma, min_child_weight;
+  int32_t max_depth, sg, sh;
+} cb_tree_params;
+
+typedef struct {
+  float loss_chg;
+  int32_t feature; /* -1: no candidate */
+  int32_t split_bin;
+  int32_t default_left;
+  float threshold;
+  int32_t pad_;
+  int64_t GL, HL, GR, HR;
+} cb_split;
+
+/* totals: int64 [2] (G, H of the node); feature_mask: u8 [f] or NULL; out: one cb_split (device). */
+int cb_split_scan(const int64_t* hist, const int32_t* bin_ptr, int n_features, const float* cuts,
+                  const float* min_vals, const int64_t* totals, const cb_tree_params* params,
+                  const uint8_t* feature_mask, cb_split* out, void* workspace, size_t workspace_bytes,
+                  void* stream);
+int cb_split_scan_workspace_bytes(int n_features, size_t* bytes);
+
+/* ---- K6 stable row partition by compaction (R8).  Replaces RowPartitioner.
+ * seg_in/seg_out: u32 [count]; n_left: int64 [1] (device). */
+int cb_partition_workspace_bytes(int64_t count, size_t* bytes);
+int cb_partition_stable(const uint8_t* bins, int64_t ldb, const uint32_t* seg_in, int64_t count, int feature,
+                        int split_bin, int default_left, uint32_t* seg_out, int64_t* n_left, void* workspace,
+                        size_t workspace_bytes, void* stream);
+
+/* ---- K8 batched ensemble traversal (R11).  Replaces Booster.predict behind
+ * predict_proba (src/api/cobalt_fast_api.py:91, src/model_train_test/model_tree_train_test.py:171-172).
+ * nodes: packed 8-byte nodes {f32 cond; u32 meta} (meta: bits 0-14 feature, bit 15 default_left,
+ * bits 16-31 left child relative to the tree start, 0 = leaf; right = left + 1).
+ * tree_off: i32 [n_trees + 1].  out_margin and out_proba may each be NULL. */
+int cb_predict(const float* X, int64_t n_rows, int n_features, int64_t ldx, const uint64_t* nodes,
+               const int32_t* tree_off, int n_trees, float base_margin, float* out_margin, float* out_proba,
+               void* stream);
+
+/* ---- fused trainer: one boosting round = K3 + per level (K4, K9, K5, K6) + K7, with every
+ * split decision kept on the device (no host synchronisation inside a tree).
+ * Replaces the body of XGBClassifier.fit's boosting loop. */
+typedef struct {
+  int64_t n_rows;     /* rows on this rank */
+  int64_t ldb;
+  int64_t row_offset; /* global index of local row 0 (row sampling is a function of the global row) */
+  int32_t n_features;
+  int32_t total_bins;
+  int32_t max_trees;  /* forest capacity (rows of the forest arrays) */
+  int32_t world_size; /* >1: the caller sums the level buffer over ranks between level_hist and level_split */
+  cb_tree_params tree;
+  float scale_pos_weight;
+  uint32_t keep_thresh;
+  uint32_t seed;
+  int32_t pad_;
+} cb_train_config;
+
+typedef struct {
+  const uint8_t* bins;     /* [n][ldb] */
+  const uint8_t* y;        /* [n] */
+  const float* weight;     /* [n] or NULL */
+  float* margin;           /* [n] in/out */
+  const int32_t* bin_ptr;  /* [f+1] */
+  const float* cuts;       /* [f][256] */
+  const float* min_vals;   /* [f] */
+  /* forest out, each [max_trees][max_nodes], max_nodes = 2^(max_depth+1)-1 (wire format a-9) */
+  int32_t* left; int32_t* right; int32_t* parent; int32_t* split_index; int32_t* split_bin;
+  float* split_cond; uint8_t* default_left; float* base_weight; float* loss_chg; float* sum_hess;
+  int32_t* n_nodes;        /* [max_trees] */
+} cb_train_buffers;
+
+typedef struct cb_trainer_s cb_trainer;
+
+int cb_trainer_workspace_bytes(const cb_train_config* cfg, size_t* bytes);
+int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, void* workspace,
+                      size_t workspace_bytes, cb_trainer** out);
+void cb_trainer_destroy(cb_trainer* tr);
+/* whole round on one GPU; feature_mask: u8 [f] (device) or NULL (colsample_bytree) */
+int cb_trainer_boost_round(cb_trainer* tr, int tree_index, const uint8_t* feature_mask, void* stream);
+/* the same round in steps, for row-sharded training:
+ *   round_begin; for level in 0..max_depth-1: level_hist, <allreduce level buffer>, level_split; round_end */
+int cb_trainer_round_begin(cb_trainer* tr, int tree_index, const uint8_t* feature_mask, void* stream);
+int cb_trainer_level_hist(cb_trainer* tr, int level, void* stream);
+int cb_trainer_level_split(cb_trainer* tr, int level, void* stream);
+int cb_trainer_round_end(cb_trainer* tr, void* stream);
+/* int64 buffer to sum over ranks after level_hist(level): pointer and element count */
+int cb_trainer_level_buffer(cb_trainer* tr, int level, int64_t** ptr, int64_t* n_values);
+/* introspection for parity tests: current row order u32 [n], histogram pool slot of a node */
+int cb_trainer_row_order(cb_trainer* tr, const uint32_t** ptr);
+int cb_trainer_node_hist(cb_trainer* tr, int node_id, const int64_t** ptr);
+/* measurement hooks (bench.py): CUDA events around the histogram kernels of level_hist.
+ * last_hist_timing_sync blocks until the last level_hist finished and also returns the rows it scanned. */
+int cb_trainer_enable_timing(cb_trainer* tr, int on);
+int cb_trainer_last_hist_timing_sync(cb_trainer* tr, float* ms_accum, float* ms_reduce, int64_t* rows, int* n_build);
+/* kernels launched by this trainer so far (bench.py's gpu_launches) */
+int64_t cb_trainer_launch_count(cb_trainer* tr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COBALT_GBDT_H_ */

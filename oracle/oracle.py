@@ -266,3 +266,34 @@ def calc_gain(G, H, lam=1.0, alpha=0.0, mcw=0.0) -> float:
 
 def calc_weight(G, H, lam=1.0, alpha=0.0, mcw=0.0) -> float:
     return float(lib().orc_calc_weight(float(G), float(H), lam, alpha, mcw))
+
+
+def fit_reference(X, y, *, n_estimators=100, max_depth=6, learning_rate=0.3, scale_pos_weight=1.0, gamma=0.0,
+                  reg_lambda=1.0, reg_alpha=0.0, min_child_weight=1.0, max_bin=256, subsample=1.0, seed=0,
+                  feature_masks=None, base_score=None, sample_weight=None, ldb=None, want_rows=False,
+                  want_hist=False):
+    """The whole reference path on the CPU: cuts -> bins -> boosting rounds (R1..R10)."""
+    X = np.ascontiguousarray(X, np.float32)
+    y = np.ascontiguousarray(y, np.uint8)
+    n, f = X.shape
+    cuts, n_cuts, min_vals = compute_cuts(X, max_bin)
+    bins = bin_matrix(X, cuts, n_cuts, ldb=ldb or (f + 15) // 16 * 16)
+    bp = bin_ptr_of(n_cuts)
+    wmax = 1.0 if sample_weight is None else float(np.max(sample_weight))
+    sg, sh = quant_shifts(max(1.0, float(scale_pos_weight)) * wmax)
+    if base_score is None:
+        base_score = estimate_base_score(y, scale_pos_weight, sample_weight)
+    tp = TreeParams(eta=float(np.float32(learning_rate)), reg_lambda=reg_lambda, reg_alpha=reg_alpha, gamma=gamma,
+                    min_child_weight=min_child_weight, max_depth=max_depth, sg=sg, sh=sh)
+    margin = np.full(n, base_margin_of(base_score), np.float32)
+    fo = train(bins, f, bp, cuts, min_vals, y, sample_weight, float(scale_pos_weight), tp, n_estimators, margin,
+               subsample=subsample, seed=seed, feature_masks=feature_masks, want_rows=want_rows, want_hist=want_hist)
+    return {"cuts": cuts, "n_cuts": n_cuts, "min_vals": min_vals, "bins": bins, "bin_ptr": bp, "forest": fo,
+            "flat": flatten_forest(fo), "margin": margin, "base_score": base_score, "sg": sg, "sh": sh, "tp": tp}
+
+
+def predict_proba_reference(fit: dict, X) -> np.ndarray:
+    ff = fit["flat"]
+    m = predict_margin(X, ff["tree_offsets"], ff["left"], ff["right"], ff["split_index"], ff["split_cond"],
+                       ff["default_left"], base_margin_of(fit["base_score"]))
+    return sigmoid(m)

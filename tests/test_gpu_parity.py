@@ -1,0 +1,419 @@
+"""GPU parity suite (-m gpu): every CUDA entry point is called through the C ABI
+(cobalt_smart_lender_ai_b200.ops / trainer -> ctypes -> libcobalt_gbdt.so) and compared with
+the CPU oracle on the same seeded inputs.  Integer, byte and index results must be
+bit-exact; probabilities within 1e-5 (they are in fact bit-equal); AUC within 1e-4."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from cobalt_smart_lender_ai_b200 import ops as _ops
+    return _ops
+
+
+@pytest.fixture(scope="module")
+def data():
+    from cobalt_smart_lender_ai_b200.synth import make_lending
+    X, y, names = make_lending(60000, 60, seed=7)
+    return X.numpy(), y.numpy(), names
+
+
+def _dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _edge_matrix(n=5003, seed=3):
+    rng = np.random.default_rng(seed)
+    X = np.zeros((n, 11), np.float32)
+    X[:, 0] = rng.normal(size=n)
+    X[:, 1] = np.nan                                   # empty column
+    X[:, 2] = 3.25                                     # constant
+    X[:, 3] = rng.integers(0, 2, n)                    # binary
+    X[:, 4] = rng.integers(-5, 12, n)                  # few distinct, negatives
+    X[:, 5] = np.where(rng.random(n) < 0.5, -0.0, 0.0) # signed zeros
+    X[:, 6] = rng.lognormal(3, 2, n)
+    X[:, 7] = np.round(rng.normal(size=n) * 40)        # ~250 distinct: around the 255 limit
+    X[:, 8] = np.round(rng.normal(size=n) * 60)        # > 255 distinct with heavy ties
+    X[:, 9] = rng.normal(size=n) * 1e30
+    X[:, 10] = rng.integers(0, 300, n)                 # exactly 300 distinct
+    X[rng.random(X.shape) < 0.07] = np.nan
+    X[0, 0], X[1, 0], X[2, 6] = np.inf, -np.inf, np.inf
+    return X
+
+
+@pytest.mark.parametrize("max_bin", [256, 16, 2])
+def test_sketch_cuts_bit_exact(ops, max_bin):
+    X = _edge_matrix()
+    cuts, nc, mv = O.compute_cuts(X, max_bin)
+    c, k, m = ops.sketch_cuts(_dev(X), max_bin)
+    assert np.array_equal(k.cpu().numpy(), nc)
+    assert np.array_equal(m.cpu().numpy().view(np.uint32), mv.view(np.uint32))
+    assert np.array_equal(c.cpu().numpy().view(np.uint32), cuts.view(np.uint32))
+
+
+def test_sketch_cuts_schema(ops, data):
+    X = data[0]
+    cuts, nc, mv = O.compute_cuts(X, 256)
+    c, k, m = ops.sketch_cuts(_dev(X), 256)
+    assert np.array_equal(k.cpu().numpy(), nc)
+    assert np.array_equal(c.cpu().numpy().view(np.uint32), cuts.view(np.uint32))
+    assert np.array_equal(m.cpu().numpy().view(np.uint32), mv.view(np.uint32))
+
+
+@pytest.mark.parametrize("n", [1, 31, 4097])
+def test_sketch_ragged_sizes(ops, n):
+    X = _edge_matrix(n=max(n, 8))[:n]
+    cuts, nc, mv = O.compute_cuts(X, 256)
+    c, k, m = ops.sketch_cuts(_dev(X), 256)
+    assert np.array_equal(k.cpu().numpy(), nc)
+    assert np.array_equal(c.cpu().numpy().view(np.uint32), cuts.view(np.uint32))
+
+
+def test_bin_pack_bit_exact(ops, data):
+    for X in (_edge_matrix(), data[0][:20011]):
+        cuts, nc, _ = O.compute_cuts(X, 256)
+        ldb = ops.padded_ldb(X.shape[1])
+        want = O.bin_matrix(X, cuts, nc, ldb=ldb)
+        got = ops.bin_pack(_dev(X), _dev(cuts), _dev(nc), ldb).cpu().numpy()
+        assert np.array_equal(got, want)
+
+
+def test_sigmoid_and_grad_bit_exact(ops):
+    rng = np.random.default_rng(0)
+    m = np.concatenate([rng.normal(size=100000) * 6, [0, -0.0, 100, -100, 88.7, -87.1, 1e-30]]).astype(np.float32)
+    assert np.array_equal(ops.sigmoid(_dev(m)).cpu().numpy().view(np.uint32), O.sigmoid(m).view(np.uint32))
+    y = (rng.random(len(m)) < 0.13).astype(np.uint8)
+    w = rng.random(len(m)).astype(np.float32) + 0.5
+    for weight, sub in ((None, 1.0), (w, 1.0), (None, 0.8)):
+        wmax = 1.0 if weight is None else float(weight.max())
+        sg, sh = O.quant_shifts(6.75 * wmax)
+        assert (sg, sh) == ops.quant_shifts(6.75 * wmax)
+        want = O.grad(m, y, weight, 6.75, sg, sh, subsample=sub, seed=78, tree=3, row_offset=1000)
+        gp, tot = ops.grad_logistic(_dev(m), _dev(y), None if weight is None else _dev(weight), 6.75, sg, sh,
+                                    subsample=sub, seed=78, tree=3, row_offset=1000)
+        assert np.array_equal(gp.cpu().numpy(), want)
+        assert tot.cpu().numpy().tolist() == want.astype(np.int64).sum(0).tolist()
+        assert np.abs(want).max() <= 2 ** 18
+
+
+def _binned(ops, X):
+    cuts, nc, mv = O.compute_cuts(X, 256)
+    ldb = ops.padded_ldb(X.shape[1])
+    bins = O.bin_matrix(X, cuts, nc, ldb=ldb)
+    return cuts, nc, mv, bins, O.bin_ptr_of(nc)
+
+
+def test_hist_build_bit_exact(ops, data):
+    X, y, _ = data
+    cuts, nc, mv, bins, bp = _binned(ops, X)
+    rng = np.random.default_rng(1)
+    f = X.shape[1]
+    q = O.grad(rng.normal(size=len(y)).astype(np.float32), y, None, 6.75, 15, 17)
+    bd, qd, bpd = _dev(bins), _dev(q), _dev(bp)
+    S = int(bp[-1])
+    # root (identity rows), then gathered subsets of ragged sizes incl. empty
+    assert np.array_equal(ops.hist_build(bd, f, qd, None, bpd, S).cpu().numpy(), O.hist(bins, f, q, None, bp))
+    for cnt in (0, 1, 33, 4096, 4097, 25001):
+        rows = np.sort(rng.choice(len(y), cnt, replace=False)).astype(np.uint32)
+        got = ops.hist_build(bd, f, qd, _dev(rows.view(np.int32)) if cnt else torch.zeros(0, dtype=torch.int32, device="cuda"),
+                             bpd, S, count=cnt).cpu().numpy()
+        assert np.array_equal(got, O.hist(bins, f, q, rows, bp)), cnt
+    # additivity (K9): parent - built == sibling
+    rows = rng.permutation(len(y)).astype(np.uint32)
+    a, b = np.sort(rows[:20000]), np.sort(rows[20000:])
+    ha = ops.hist_build(bd, f, qd, _dev(a.view(np.int32)), bpd, S)
+    root = ops.hist_build(bd, f, qd, None, bpd, S)
+    assert np.array_equal(ops.hist_subtract(root, ha).cpu().numpy(), O.hist(bins, f, q, b, bp))
+
+
+def test_hist_many_bins_uses_feature_tiles(ops):
+    """150 continuous features x 255 bins = 38 250 slots: more than one shared-memory tile."""
+    rng = np.random.default_rng(2)
+    X = rng.normal(size=(9000, 150)).astype(np.float32)
+    X[rng.random(X.shape) < 0.02] = np.nan
+    cuts, nc, mv, bins, bp = _binned(ops, X)
+    assert bp[-1] > 30000
+    y = (rng.random(9000) < 0.2).astype(np.uint8)
+    q = O.grad(np.zeros(9000, np.float32), y, None, 4.0, 16, 18)
+    got = ops.hist_build(_dev(bins), 150, _dev(q), None, _dev(bp), int(bp[-1])).cpu().numpy()
+    assert np.array_equal(got, O.hist(bins, 150, q, None, bp))
+
+
+def _tp(ops, **kw):
+    from cobalt_smart_lender_ai_b200._lib import TreeParams
+    d = dict(eta=0.3, reg_lambda=1.0, reg_alpha=0.0, gamma=0.0, min_child_weight=1.0, max_depth=6, sg=15, sh=17)
+    d.update(kw)
+    return TreeParams(np.float32(d["eta"]), d["reg_lambda"], d["reg_alpha"], d["gamma"], d["min_child_weight"],
+                      d["max_depth"], d["sg"], d["sh"]), O.TreeParams(**d)
+
+
+def _assert_split_equal(got, want):
+    assert got["feature"] == want["feature"]
+    if want["feature"] < 0:
+        return
+    for k in ("split_bin", "default_left", "GL", "HL", "GR", "HR"):
+        assert got[k] == want[k], k
+    assert np.float32(got["loss_chg"]).view(np.uint32) == np.float32(want["loss_chg"]).view(np.uint32)
+    assert np.float32(got["threshold"]).view(np.uint32) == np.float32(want["threshold"]).view(np.uint32)
+
+
+def test_split_scan_bit_exact(ops, data):
+    X, y, _ = data
+    cuts, nc, mv, bins, bp = _binned(ops, X)
+    rng = np.random.default_rng(4)
+    f = X.shape[1]
+    q = O.grad(rng.normal(size=len(y)).astype(np.float32), y, None, 6.75, 15, 17)
+    for trial in range(6):
+        cnt = [len(y), 30000, 5000, 700, 60, 5][trial]
+        rows = None if trial == 0 else np.sort(rng.choice(len(y), cnt, replace=False)).astype(np.uint32)
+        h = O.hist(bins, f, q, rows, bp)
+        tot = q.astype(np.int64).sum(0) if rows is None else q[rows].astype(np.int64).sum(0)
+        for kw in (dict(), dict(reg_alpha=0.5, min_child_weight=3.0), dict(reg_lambda=0.0, min_child_weight=0.0)):
+            tpc, tpo = _tp(ops, **kw)
+            mask = None if trial % 2 == 0 else (rng.random(f) < 0.6).astype(np.uint8)
+            want = O.scan(h, bp, cuts, mv, tot[0], tot[1], tpo, mask)
+            got = ops.split_scan(_dev(h), _dev(bp), _dev(cuts), _dev(mv), _dev(tot), tpc,
+                                 None if mask is None else _dev(mask))
+            _assert_split_equal(got, want)
+
+
+def test_split_scan_ties_and_missing(ops):
+    bp = np.array([0, 3, 6], np.int32)
+    cuts = np.full((2, 256), np.inf, np.float32)
+    cuts[:, :3] = [1, 2, 3]
+    mv = np.array([-1, -1], np.float32)
+    tpc, tpo = _tp(ops, eta=1.0, min_child_weight=0.0, max_depth=3, sg=4, sh=4)
+    cases = [
+        (np.array([[-160, 160], [0, 160], [160, 160]] * 2, np.int64), (0, 480)),
+        (np.array([[-160, 160], [160, 160], [0, 0], [0, 16], [0, 16], [0, 16]], np.int64), (-480, 640)),
+        (np.zeros((6, 2), np.int64), (0, 0)),
+    ]
+    for h, tot in cases:
+        t = np.array(tot, np.int64)
+        _assert_split_equal(ops.split_scan(_dev(h), _dev(bp), _dev(cuts), _dev(mv), _dev(t), tpc),
+                            O.scan(h, bp, cuts, mv, t[0], t[1], tpo))
+
+
+@pytest.mark.parametrize("cnt", [0, 1, 31, 32, 33, 2047, 2048, 2049, 50021])
+def test_partition_stable_bit_exact(ops, data, cnt):
+    X = data[0]
+    cuts, nc, mv, bins, bp = _binned(ops, X)
+    rng = np.random.default_rng(cnt)
+    seg = np.sort(rng.choice(len(X), cnt, replace=False)).astype(np.uint32)
+    bd = _dev(bins)
+    for feat, sb, dl in ((0, 100, 0), (1, 30, 1), (40, 0, 0), (33, -1, 1), (59, 0, 1)):
+        want, nl = O.partition(bins, seg, feat, sb, dl)
+        got, gl = ops.partition_stable(bd, _dev(seg.view(np.int32)) if cnt else torch.zeros(0, dtype=torch.int32, device="cuda"),
+                                       feat, sb, dl)
+        assert gl == nl
+        assert np.array_equal(got.cpu().numpy().view(np.uint32), want)
+
+
+def _train_gpu(ops, ref, X, y, n_trees, spw, subsample=1.0, seed=0, masks=None, weight=None, **kw):
+    from cobalt_smart_lender_ai_b200.trainer import GpuTrainer
+    tp = ref["tp"]
+    bins = _dev(ref["bins"])
+    tr = GpuTrainer(bins, _dev(y), None if weight is None else _dev(weight), X.shape[1], _dev(ref["bin_ptr"]),
+                    _dev(ref["cuts"]), _dev(ref["min_vals"]), max_depth=tp.max_depth, eta=tp.eta,
+                    reg_lambda=tp.reg_lambda, reg_alpha=tp.reg_alpha, gamma=tp.gamma,
+                    min_child_weight=tp.min_child_weight, scale_pos_weight=spw, sg=tp.sg, sh=tp.sh,
+                    subsample=subsample, seed=seed, max_trees=n_trees, base_margin=O.base_margin_of(ref["base_score"]),
+                    group=False)
+    tr.boost(n_trees, None if masks is None else _dev(masks))
+    return tr
+
+
+def _assert_forest_equal(got, want_flat):
+    assert np.array_equal(got["tree_offsets"], want_flat["tree_offsets"])
+    for k in ("left", "right", "parent", "split_index", "split_bin", "default_left"):
+        assert np.array_equal(got[k], want_flat[k]), k
+    for k in ("split_cond", "base_weight", "loss_chg", "sum_hess"):
+        assert np.array_equal(got[k].view(np.uint32), want_flat[k].view(np.uint32)), k
+
+
+def _final_rows(ref, tr, bins):
+    """GPU rows are not moved at the last level (children are leaves): finish the stable
+    partition of the last level on the host before comparing with the oracle's row order."""
+    rows = tr.row_order()
+    rows = np.arange(tr.n, dtype=np.uint32) if rows is None else rows.cpu().numpy().view(np.uint32).copy()
+    fo = tr.forest_numpy()
+    t = tr.n_trees - 1
+    a = int(fo["tree_offsets"][t])
+    D = tr.max_depth
+    # walk the tree to find depth-(D-1) internal nodes and their segments
+    L, R = fo["left"][a:], fo["right"][a:]
+    segs = {0: (0, tr.n)}
+    depth = {0: 0}
+    order = [0]
+    for nid in order:
+        if L[nid] < 0:
+            continue
+        b, c = segs[nid]
+        seg = rows[b:b + c]
+        if depth[nid] == D - 1:
+            out, nl = O.partition(bins, seg, int(fo["split_index"][a + nid]), int(fo["split_bin"][a + nid]),
+                                  int(fo["default_left"][a + nid]))
+            rows[b:b + c] = out
+            continue
+        code = bins[seg.astype(np.int64), int(fo["split_index"][a + nid])]
+        left = np.where(code == 255, bool(fo["default_left"][a + nid]), code <= fo["split_bin"][a + nid])
+        nl = int(left.sum())
+        segs[L[nid]], segs[R[nid]] = (b, nl), (b + nl, c - nl)
+        depth[L[nid]] = depth[R[nid]] = depth[nid] + 1
+        order += [L[nid], R[nid]]
+    return rows
+
+
+def test_train_matches_committed_golden(ops, oracle_small):
+    g = oracle_small
+    X, y = g["X"], g["y"]
+    ref = O.fit_reference(X, y, n_estimators=5, max_depth=4, scale_pos_weight=float(g["spw"]), base_score=0.5,
+                          ldb=32, want_rows=True, want_hist=True)
+    assert np.array_equal(ref["forest"]["split_index"], g["forest_split_index"])
+    tr = _train_gpu(ops, ref, X, y, 5, float(g["spw"]))
+    _assert_forest_equal(tr.forest_numpy(), ref["flat"])
+    assert np.array_equal(tr.margin.cpu().numpy().view(np.uint32), g["margin"].view(np.uint32))
+    assert np.array_equal(tr.node_hist(0).cpu().numpy(), g["forest_root_hist"])
+    assert np.array_equal(_final_rows(ref, tr, g["bins"]), g["forest_row_order"])
+
+
+@pytest.mark.parametrize("cfg", [
+    dict(n_estimators=12, max_depth=6),
+    dict(n_estimators=6, max_depth=3, learning_rate=0.05, gamma=5.0),
+    dict(n_estimators=5, max_depth=8, min_child_weight=5.0, reg_lambda=0.5, reg_alpha=0.1),
+    dict(n_estimators=6, max_depth=5, subsample=0.8, seed=78),
+    dict(n_estimators=3, max_depth=1),
+])
+def test_train_bit_exact(ops, data, cfg):
+    X, y, _ = data
+    spw = float((y == 0).sum() / (y == 1).sum())
+    ref = O.fit_reference(X, y, scale_pos_weight=spw, want_rows=True, want_hist=True, **cfg)
+    tr = _train_gpu(ops, ref, X, y, cfg["n_estimators"], spw, subsample=cfg.get("subsample", 1.0), seed=cfg.get("seed", 0))
+    _assert_forest_equal(tr.forest_numpy(), ref["flat"])
+    assert np.array_equal(tr.margin.cpu().numpy().view(np.uint32), ref["margin"].view(np.uint32))
+    assert np.array_equal(tr.node_hist(0).cpu().numpy(), ref["forest"]["root_hist"])
+    assert np.array_equal(_final_rows(ref, tr, ref["bins"]), ref["forest"]["row_order"])
+
+
+def test_train_colsample_and_weights(ops, data):
+    from cobalt_smart_lender_ai_b200.sklearn import colsample_masks
+    X, y, _ = data
+    X, y = X[:20000], y[:20000]
+    rng = np.random.default_rng(9)
+    w = (rng.random(len(y)) + 0.25).astype(np.float32)
+    masks = colsample_masks(4, X.shape[1], 0.5, 78)
+    ref = O.fit_reference(X, y, n_estimators=4, max_depth=5, scale_pos_weight=3.0, feature_masks=masks, sample_weight=w)
+    tr = _train_gpu(ops, ref, X, y, 4, 3.0, masks=masks, weight=w)
+    _assert_forest_equal(tr.forest_numpy(), ref["flat"])
+    assert np.array_equal(tr.margin.cpu().numpy().view(np.uint32), ref["margin"].view(np.uint32))
+
+
+def test_predict_fixture_forest(ops, fixture_forest):
+    """The reference's shipped 300-tree model scored on the GPU vs the oracle (R11)."""
+    from cobalt_smart_lender_ai_b200.booster import Booster
+    ff = fixture_forest
+    rng = np.random.default_rng(5)
+    internal = ff["left"] != -1
+    X = np.zeros((4099, 20), np.float32)
+    for j in range(20):
+        tj = ff["split_cond"][internal & (ff["split_index"] == j)]
+        X[:, j] = rng.choice(tj, size=len(X)) + rng.choice([-1e-3, 0.0, 1e-3], size=len(X))
+    X[rng.random(X.shape) < 0.1] = np.nan
+    want = O.predict_margin(X, ff["tree_offsets"], ff["left"], ff["right"], ff["split_index"], ff["split_cond"],
+                            ff["default_left"], 0.0)
+    b = Booster(ff, 20, [str(s) for s in ff["feature_names"]], float(ff["base_score"]))
+    got = b.predict_device(_dev(X), output_margin=True).cpu().numpy()
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    p = b.predict_device(_dev(X)).cpu().numpy()
+    assert np.max(np.abs(p - O.sigmoid(want))) <= 1e-5
+    # ragged: 0 rows and 1 row
+    assert b.predict_device(_dev(X[:1])).shape == (1,)
+    assert b.predict_device(_dev(X[:0])).shape == (0,)
+
+
+def test_estimator_end_to_end(ops, data):
+    """fit/predict_proba/predict/feature_importances_/get_score/pickle through the drop-in class."""
+    import pickle
+
+    import pandas as pd
+    from sklearn.metrics import roc_auc_score
+
+    from cobalt_smart_lender_ai_b200.sklearn import XGBClassifier
+    X, y, names = data
+    df = pd.DataFrame(X[:40000], columns=names)
+    for c in names[-5:]:
+        df[c] = df[c].astype(bool)               # get_dummies emits bool columns
+    yt = pd.Series(y[:40000])
+    spw = float((yt == 0).sum() / (yt == 1).sum())
+    clf = XGBClassifier(eval_metric="logloss", use_label_encoder=False, scale_pos_weight=spw, random_state=42,
+                        n_estimators=20)
+    clf.fit(df, yt)
+    ref = O.fit_reference(X[:40000], y[:40000], n_estimators=20, max_depth=6, learning_rate=0.3, scale_pos_weight=spw)
+    _assert_forest_equal(clf.get_booster().forest | {"split_bin": ref["flat"]["split_bin"]}, ref["flat"])
+    Xt, ytest = X[40000:], y[40000:]
+    proba = clf.predict_proba(pd.DataFrame(Xt, columns=names))
+    want = O.predict_proba_reference(ref, Xt)
+    assert proba.shape == (len(Xt), 2) and proba.dtype == np.float32
+    assert np.max(np.abs(proba[:, 1] - want)) <= 1e-5
+    assert abs(roc_auc_score(ytest, proba[:, 1]) - roc_auc_score(ytest, want)) <= 1e-4
+    assert np.array_equal(clf.predict(Xt), (want > 0.5).astype(np.int64))
+    imp = clf.feature_importances_
+    assert imp.shape == (60,) and abs(imp.sum() - 1.0) < 1e-5
+    gain = clf.get_booster().get_score(importance_type="gain")
+    fo = ref["flat"]
+    internal = fo["left"] >= 0
+    j = int(fo["split_index"][0])
+    sel = internal & (fo["split_index"] == j)
+    assert gain[names[j]] == pytest.approx(float(fo["loss_chg"][sel].astype(np.float64).mean()))
+    clf2 = pickle.loads(pickle.dumps(clf))
+    assert np.array_equal(clf2.predict_proba(Xt[:100]), proba[:100])
+    with pytest.raises(ValueError):
+        clf.predict_proba(pd.DataFrame(Xt[:5], columns=names[::-1]))
+
+
+def test_full_size_properties(ops):
+    """BASELINE size (2.2M x 150): properties that need no oracle run -- histogram additivity
+    (parent = left + right, exact), node totals, margin replay through the scoring kernel."""
+    from cobalt_smart_lender_ai_b200.sklearn import XGBClassifier
+    from cobalt_smart_lender_ai_b200.synth import make_lending
+    from cobalt_smart_lender_ai_b200.trainer import GpuTrainer
+    n, f = 2_200_000, 150
+    X, y, _ = make_lending(n, f, device="cuda")
+    cuts, n_cuts, min_vals = ops.sketch_cuts(X, 256)
+    bins = ops.bin_pack(X, cuts, n_cuts)
+    bp = ops.bin_ptr_of(n_cuts)
+    spw = float(((y == 0).sum() / (y == 1).sum()).item())
+    sg, sh = ops.quant_shifts(spw)
+    tr = GpuTrainer(bins, y, None, f, bp, cuts, min_vals, max_depth=6, eta=0.3, scale_pos_weight=spw, sg=sg, sh=sh,
+                    max_trees=3, group=False)
+    tr.boost(3)
+    fo = tr.forest_numpy()
+    a = int(fo["tree_offsets"][2])
+    L, R = fo["left"][a:], fo["right"][a:]
+    checked = 0
+    for nid in range(len(L)):
+        if L[nid] >= 0 and R[nid] < 63:          # children with a histogram slot (depth < 6)
+            hp, hl, hr = tr.node_hist(nid), tr.node_hist(int(L[nid])), tr.node_hist(int(R[nid]))
+            assert torch.equal(hp, hl + hr)
+            checked += 1
+    assert checked >= 20
+    # every feature's bins + its missing rows sum to the node total: check the dense last one-hot column
+    root = tr.node_hist(0)
+    b0, b1 = int(bp[f - 1]), int(bp[f])
+    gp, tot = ops.grad_logistic(torch.zeros(1, device="cuda"), y[:1], None, spw, sg, sh)  # smoke of the standalone call
+    assert root[b0:b1].sum(0).tolist() == root[int(bp[f - 2]):b0].sum(0).tolist()
+    # margin replay: scoring kernel on raw floats == training-time margins on bins (bit-exact)
+    from cobalt_smart_lender_ai_b200.booster import Booster
+    m = Booster(fo, f, None, 0.5).predict_device(X, output_margin=True)
+    assert torch.equal(m.view(torch.int32), tr.margin.view(torch.int32))
+    # the sorted-ness property of the stable partition: every leaf segment is ascending in row id
+    rows = tr.row_order().cpu().numpy().view(np.uint32)
+    assert np.array_equal(np.sort(rows), np.arange(n, dtype=np.uint32))
