@@ -238,8 +238,8 @@ int cb_partition_workspace_bytes(int64_t count, size_t* bytes) {
 int cb_partition_stable(const uint8_t* bins, int64_t ldb, const uint32_t* seg_in, int64_t count, int feature,
                         int split_bin, int default_left, uint32_t* seg_out, int64_t* n_left, void* ws,
                         size_t ws_bytes, void* stream) {
-  if (!bins || !seg_in || !seg_out || !n_left || !ws || count < 0 || feature < 0 || feature >= ldb ||
-      count > 2147483647LL)
+  if (!bins || !n_left || !ws || count < 0 || feature < 0 || feature >= ldb || count > 2147483647LL ||
+      (count > 0 && (!seg_in || !seg_out)))
     return fail(CB_ERR_INVALID, "cb_partition_stable: bad arguments");
   size_t need = 0;
   cb_partition_workspace_bytes(count, &need);
@@ -263,9 +263,9 @@ int cb_partition_stable(const uint8_t* bins, int64_t ldb, const uint32_t* seg_in
 // ---------------------------------------------------------------------------- K8
 int cb_predict(const float* X, int64_t n, int f, int64_t ldx, const uint64_t* nodes, const int32_t* tree_off,
                int n_trees, float base_margin, float* out_margin, float* out_proba, void* stream) {
+  if (n == 0) return CB_OK;
   if (!X || !nodes || !tree_off || n < 0 || f <= 0 || f > 32767 || ldx < f || n_trees < 0 || (!out_margin && !out_proba))
     return fail(CB_ERR_INVALID, "cb_predict: bad arguments");
-  if (n == 0) return CB_OK;
   DeviceInfo di;
   int rc = device_info(&di);
   if (rc) return rc;
