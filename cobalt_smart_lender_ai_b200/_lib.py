@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(_PKG, "libcobalt_gbdt.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
 
-CB_QBITS = 18
+CB_QBITS = 17
 CB_MISSING_BIN = 255
 CB_CUT_STRIDE = 256
 
@@ -47,7 +47,7 @@ class TrainConfig(C.Structure):
 
 class TrainBuffers(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in (
-        "bins", "y", "weight", "margin", "bin_ptr", "cuts", "min_vals", "left", "right", "parent", "split_index",
+        "bins", "y", "weight", "margin", "bin_ptr", "cuts", "min_vals", "pos_feature", "left", "right", "parent", "split_index",
         "split_bin", "split_cond", "default_left", "base_weight", "loss_chg", "sum_hess", "n_nodes")]
 
 
@@ -84,7 +84,8 @@ _SIGS = {
     "cb_device_info": (C.c_int, [C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "cb_sketch_workspace_bytes": (C.c_int, [_I64, _I, C.POINTER(_SZ)]),
     "cb_sketch_cuts": (C.c_int, [_VP, _I64, _I, _I64, _I, _VP, _VP, _VP, _VP, _SZ, _VP]),
-    "cb_bin_pack_u8": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _VP, _I64, _VP]),
+    "cb_plan_layout": (C.c_int, [_VP, _I, _I64, _VP, C.POINTER(C.c_int32)]),
+    "cb_bin_pack_u8": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _VP, _VP, _I64, _VP]),
     "cb_grad_logistic_q": (C.c_int, [_VP, _VP, _VP, _I64, _F, _I, _I, _U32, _U32, _U32, _I64, _VP, _VP, _VP]),
     "cb_sigmoid": (C.c_int, [_VP, _I64, _VP, _VP]),
     "cb_hist_workspace_bytes": (C.c_int, [_I64, _I, C.POINTER(_SZ)]),

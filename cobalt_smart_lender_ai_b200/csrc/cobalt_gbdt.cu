@@ -2,6 +2,7 @@
 #include <new>
 
 #include "sketch.cuh"
+#include "hist_cf.cuh"
 #include "trainer.cuh"
 
 namespace cb {
@@ -68,14 +69,35 @@ int cb_device_info(int* sm_count, int* smem_optin_bytes) {
 }
 
 // ---------------------------------------------------------------------------- K2
+int cb_plan_layout(const int32_t* n_cuts_host, int f, int64_t ldb, int32_t* pos_feature_host, int32_t* conflict_free) {
+  if (!n_cuts_host || !pos_feature_host || f <= 0 || ldb < f || (ldb & 3))
+    return fail(CB_ERR_INVALID, "cb_plan_layout: bad arguments");
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  std::vector<int32_t> bp((size_t)f + 1, 0);
+  for (int i = 0; i < f; ++i) {
+    if (n_cuts_host[i] < 1 || n_cuts_host[i] > CB_MAX_BINS) return fail(CB_ERR_INVALID, "cb_plan_layout: n_cuts[%d] out of range", i);
+    bp[i + 1] = bp[i] + n_cuts_host[i];
+  }
+  plan_positions(n_cuts_host, f, ldb, pos_feature_host);
+  CfHostTables tb;
+  const bool ok = build_cf_tables(bp.data(), pos_feature_host, f, ldb, hist_budget_slots(di) * 8, &tb);
+  if (!ok) {                       // does not fit one shared-memory image: natural column order, tiled kernel
+    for (int64_t p = 0; p < ldb; ++p) pos_feature_host[p] = p < f ? (int32_t)p : -1;
+  }
+  if (conflict_free) *conflict_free = ok ? 1 : 0;
+  return CB_OK;
+}
+
 int cb_bin_pack_u8(const float* X, int64_t n, int f, int64_t ldx, const float* cuts, const int32_t* n_cuts,
-                   uint8_t* bins, int64_t ldb, void* stream) {
+                   const int32_t* pos_feature, uint8_t* bins, int64_t ldb, void* stream) {
   if (!X || !cuts || !n_cuts || !bins || n < 0 || f <= 0 || ldx < f || ldb < f || (ldb & 3))
     return fail(CB_ERR_INVALID, "cb_bin_pack_u8: bad arguments (ldb must be a multiple of 4 and >= n_features)");
   if (n == 0) return CB_OK;
   int wpr = (int)(ldb / 4);
   int64_t items = n * wpr;
-  bin_pack_kernel<<<ceil_div(items, 256), 256, 0, (cudaStream_t)stream>>>(X, n, f, ldx, cuts, n_cuts,
+  bin_pack_kernel<<<ceil_div(items, 256), 256, 0, (cudaStream_t)stream>>>(X, n, f, ldx, cuts, n_cuts, pos_feature,
                                                                          reinterpret_cast<uint32_t*>(bins), wpr);
   CB_LAUNCH_CHECK();
   return CB_OK;
@@ -308,6 +330,15 @@ struct cb_trainer_s {
   int64_t launches;
   bool timing;
   cudaEvent_t ev[3];
+  // conflict-free histogram path
+  bool cf;
+  int cf_R, cf_smem;
+  CfLayout* cf_lay;
+  int32_t* cf_slot_of;
+  int32_t* cf_fold_src;
+  int32_t* cf_fold_dst;
+  int32_t* feat_pos;      // [f] byte position of a feature inside a binned row
+  int part_words;         // int32 words per partial histogram
 };
 
 static int trainer_layout(const cb_train_config* cfg, const DeviceInfo& di, void* ws, cb_trainer_s* t, size_t* bytes) {
@@ -334,14 +365,23 @@ static int trainer_layout(const cb_train_config* cfg, const DeviceInfo& di, void
   na.H = b.take<long long>((size_t)max_nodes);
   int64_t* pool = b.take<int64_t>((size_t)pool_slots * 2 * S);
   int64_t* level_buf = b.take<int64_t>((size_t)lb_slots * 2 * S + 2);
-  int32_t* partials = b.take<int32_t>((size_t)max_partials(n, di.sm_count) * 2 * S);
+  const int cf_words = hist_budget_slots(di);                 // upper bound of R * 32
+  const int part_words = 2 * std::max(S, cf_words);
+  int32_t* partials = b.take<int32_t>((size_t)max_partials(n, di.sm_count) * part_words);
   FeatBest* feat_best = b.take<FeatBest>((size_t)lvl_nodes * cfg->n_features);
+  CfLayout* cf_lay = b.take<CfLayout>(1);
+  int32_t* cf_slot_of = b.take<int32_t>((size_t)cf_words);
+  int32_t* cf_fold_src = b.take<int32_t>((size_t)cf_words);
+  int32_t* cf_fold_dst = b.take<int32_t>((size_t)cf_words);
+  int32_t* feat_pos = b.take<int32_t>((size_t)cfg->n_features);
   if (bytes) *bytes = b.used();
   if (t) {
     t->max_nodes = max_nodes; t->S = S; t->S2 = 2 * S; t->pool_slots = pool_slots; t->lb_slots = lb_slots;
     t->gpair = gpair; t->rows[0] = r0; t->rows[1] = r1; t->flag_bits = flag_bits; t->tile_cnt = tile_cnt;
     t->st = st; t->segs = segs; t->plan = plan; t->na = na; t->pool = pool; t->level_buf = level_buf;
     t->partials = partials; t->feat_best = feat_best;
+    t->cf_lay = cf_lay; t->cf_slot_of = cf_slot_of; t->cf_fold_src = cf_fold_src; t->cf_fold_dst = cf_fold_dst;
+    t->feat_pos = feat_pos; t->part_words = part_words;
   }
   return CB_OK;
 }
@@ -398,6 +438,36 @@ int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, v
   plan_tiles_kernel<<<1, 1>>>(buf->bin_ptr, cfg->n_features, budget, t->plan);
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { delete t; return fail(CB_ERR_CUDA, "cb_trainer_create: %s", cudaGetErrorString(e)); }
+  // column placement -> conflict-free shared-memory tables (host side, one-off)
+  {
+    const int f = cfg->n_features;
+    std::vector<int32_t> bp((size_t)f + 1), pf((size_t)cfg->ldb), fp((size_t)f, -1);
+    e = cudaMemcpy(bp.data(), buf->bin_ptr, sizeof(int32_t) * (f + 1), cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && buf->pos_feature)
+      e = cudaMemcpy(pf.data(), buf->pos_feature, sizeof(int32_t) * cfg->ldb, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) { delete t; return fail(CB_ERR_CUDA, "cb_trainer_create: %s", cudaGetErrorString(e)); }
+    if (!buf->pos_feature)
+      for (int64_t p = 0; p < cfg->ldb; ++p) pf[p] = p < f ? (int32_t)p : -1;
+    if (bp[f] != cfg->total_bins) { delete t; return fail(CB_ERR_INVALID, "trainer: total_bins does not match bin_ptr"); }
+    for (int64_t p = 0; p < cfg->ldb; ++p)
+      if (pf[p] >= 0 && pf[p] < f) fp[pf[p]] = (int32_t)p;
+    for (int i = 0; i < f; ++i)
+      if (fp[i] < 0) { delete t; return fail(CB_ERR_INVALID, "trainer: pos_feature does not place feature %d", i); }
+    CfHostTables tb;
+    t->cf = build_cf_tables(bp.data(), pf.data(), f, cfg->ldb, budget * 8, &tb);
+    e = cudaMemcpy(t->feat_pos, fp.data(), sizeof(int32_t) * f, cudaMemcpyHostToDevice);
+    if (t->cf && e == cudaSuccess) {
+      t->cf_R = tb.lay.R; t->cf_smem = tb.lay.R * 32 * 8;
+      e = cudaMemcpy(t->cf_lay, &tb.lay, sizeof(CfLayout), cudaMemcpyHostToDevice);
+      if (e == cudaSuccess) e = cudaMemcpy(t->cf_slot_of, tb.slot_of.data(), sizeof(int32_t) * tb.slot_of.size(), cudaMemcpyHostToDevice);
+      if (e == cudaSuccess && tb.lay.n_fold) {
+        e = cudaMemcpy(t->cf_fold_src, tb.fold_src.data(), sizeof(int32_t) * tb.fold_src.size(), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(t->cf_fold_dst, tb.fold_dst.data(), sizeof(int32_t) * tb.fold_dst.size(), cudaMemcpyHostToDevice);
+      }
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(hist_accum_cf_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, t->cf_smem);
+    }
+    if (e != cudaSuccess) { delete t; return fail(CB_ERR_CUDA, "cb_trainer_create: %s", cudaGetErrorString(e)); }
+  }
   *out = t;
   return CB_OK;
 }
@@ -465,15 +535,30 @@ int cb_trainer_round_begin(cb_trainer* t, int tree_index, const uint8_t* feature
 int cb_trainer_level_hist(cb_trainer* t, int level, void* stream) {
   if (!t || level < 0 || level >= t->cfg.tree.max_depth) return fail(CB_ERR_INVALID, "trainer: bad level");
   cudaStream_t s = (cudaStream_t)stream;
-  if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
-  int rc = launch_hist_accum(t->cfg.n_rows ? t->buf.bins : nullptr, t->cfg.ldb, reinterpret_cast<const int32_t*>(t->gpair),
-                             t->rows[t->cur], t->identity ? 1 : 0, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S,
-                             t->grid, t->tiles, t->smem, t->partials, s);
-  if (rc) return rc;
-  if (t->timing) CB_CUDA(cudaEventRecord(t->ev[1], s));
   const int nb = level == 0 ? 1 : (1 << (level - 1));
-  hist_reduce_kernel<<<dim3(ceil_div(t->S, 256), nb), 256, 0, s>>>(t->partials, t->plan, t->S, t->level_buf);
-  if (t->timing) CB_CUDA(cudaEventRecord(t->ev[2], s));
+  if (t->cf) {
+    CB_CUDA(cudaMemsetAsync(t->level_buf, 0, sizeof(int64_t) * (size_t)nb * t->S2, s));
+    if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
+    hist_accum_cf_kernel<4><<<t->grid, 1024, t->cf_smem, s>>>(
+        reinterpret_cast<const uint32_t*>(t->buf.bins), (int)(t->cfg.ldb / 4), t->gpair, t->rows[t->cur],
+        t->identity ? 1 : 0, t->plan, t->cf_lay, t->cf_fold_src, t->cf_fold_dst, t->partials);
+    if (t->timing) CB_CUDA(cudaEventRecord(t->ev[1], s));
+    const int tiles = ceil_div(t->cf_R, 32);
+    int nz = (2 * t->di.sm_count) / (tiles * nb);
+    nz = nz < 1 ? 1 : (nz > 16 ? 16 : nz);
+    hist_reduce_cf_kernel<<<dim3(tiles, nb, nz), 256, 0, s>>>(t->partials, t->plan, t->cf_R, t->S, t->cf_slot_of,
+                                                             t->level_buf);
+    if (t->timing) CB_CUDA(cudaEventRecord(t->ev[2], s));
+  } else {
+    if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
+    int rc = launch_hist_accum(t->buf.bins, t->cfg.ldb, reinterpret_cast<const int32_t*>(t->gpair), t->rows[t->cur],
+                               t->identity ? 1 : 0, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S, t->grid, t->tiles,
+                               t->smem, t->partials, s);
+    if (rc) return rc;
+    if (t->timing) CB_CUDA(cudaEventRecord(t->ev[1], s));
+    hist_reduce_kernel<<<dim3(ceil_div(t->S, 256), nb), 256, 0, s>>>(t->partials, t->plan, t->S, t->level_buf);
+    if (t->timing) CB_CUDA(cudaEventRecord(t->ev[2], s));
+  }
   t->launches += 2;
   if (level == 0) {
     root_totals_kernel<<<1, 1, 0, s>>>(t->st, t->level_buf + t->S2);
@@ -503,7 +588,7 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   scan_level_kernel<<<dim3(ceil_div(t->cfg.n_features, 4), ln), 128, 0, s>>>(
       t->pool, t->buf.bin_ptr, t->cfg.n_features, t->S2, t->st, level, t->na, t->cfg.tree, t->fmask, t->feat_best);
   level_finish_kernel<<<1, 256, 0, s>>>(t->st, level, D, t->feat_best, t->cfg.n_features, t->buf.cuts,
-                                        t->buf.min_vals, t->cfg.tree, t->na, tree_out(t), t->segs);
+                                        t->buf.min_vals, t->cfg.tree, t->na, tree_out(t), t->segs, t->feat_pos);
   t->launches += 3;
   const uint32_t* rin = t->rows[t->cur];
   const int ident = t->identity ? 1 : 0;

@@ -116,7 +116,7 @@ __device__ __forceinline__ double calc_weight(double G, double H, const cb_tree_
   return __ddiv_rn(-t, __dadd_rn(H, (double)p.reg_lambda));
 }
 
-constexpr int kChunkRows = 4096;   // rows per int32 partial histogram: 4096 * 2^18 = 2^30 < 2^31
+constexpr int kChunkRows = 16352;  // rows per int32 partial histogram: 16352 * 2^17 < 2^31
 constexpr int kPartTile = 2048;    // positions per partition tile
 
 }  // namespace cb

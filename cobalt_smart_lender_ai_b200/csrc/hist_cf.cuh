@@ -1,0 +1,253 @@
+// K4, bank-conflict-free form.  Included by cobalt_gbdt.cu only.
+//
+// The shared-memory atomic pipe bounds the histogram build (ncu: l1tex data pipe 91 % busy,
+// 4.1 wavefronts per ATOMS with a compact slot = bin_ptr[f] + bin layout, profiles/r01).
+// Here every lane of a warp owns one shared-memory BANK: the histogram of a feature that
+// lane `l` accumulates lives at word (rowbase + bin) * 32 + l, so the 32 addresses of one
+// ATOMS instruction always fall in 32 different banks whatever the data -> 1 wavefront.
+//
+// To make that possible the columns of the binned matrix are permuted (pos_feature): a row is
+// split into column blocks of <= 32 u32 words; in block k lane l reads word (l % wk) of row
+// slot (l / wk), i.e. a narrow last block processes ck = 32 / wk rows per instruction into ck
+// private copies that are folded before the flush.  Features are dealt to words by descending
+// bin count so that bank fill is balanced.  Global histograms keep the natural feature order.
+#pragma once
+#include <algorithm>
+#include <vector>
+
+#include "kernels.cuh"
+
+namespace cb {
+
+constexpr int kCfMaxBlocks = 4;        // up to 512 features
+
+struct CfLayout {                      // device copy lives in the trainer workspace
+  int n_blocks;
+  int R;                               // shared-memory rows of 32 banks (per G and per H array)
+  int n_fold;                          // words to fold from row-slot copies into copy 0
+  int pad_;
+  int wk[kCfMaxBlocks];                // words in the block
+  int ck[kCfMaxBlocks];                // rows per warp instruction (= private copies)
+  int a0[kCfMaxBlocks][32][4];         // word index of bin 0 of the byte's feature, -1 = padding byte
+  uint32_t skipword[kCfMaxBlocks][32]; // per byte: the code that is NOT accumulated (255 = missing)
+};
+
+struct CfHostTables {
+  CfLayout lay;
+  std::vector<int32_t> slot_of;        // [R*32] global slot of a shared-memory word, -1 = none / copy
+  std::vector<int32_t> fold_src, fold_dst;
+};
+
+// column positions: features sorted by descending bin count, dealt round robin to the words of a block
+inline void plan_positions(const int32_t* n_cuts, int f, int64_t ldb, int32_t* pos_feature) {
+  std::vector<int> order(f);
+  for (int i = 0; i < f; ++i) order[i] = i;
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return n_cuts[a] > n_cuts[b]; });
+  for (int64_t p = 0; p < ldb; ++p) pos_feature[p] = -1;
+  const int W = (f + 3) / 4;
+  int next = 0;
+  for (int k = 0; k * 32 < W; ++k) {
+    const int wk = std::min(32, W - 32 * k);
+    const int take = std::min(f - next, 4 * wk);
+    for (int r = 0; r < take; ++r) {
+      const int word = r % wk, j = r / wk;
+      pos_feature[(32 * k + word) * 4 + j] = order[next + r];
+    }
+    next += take;
+  }
+}
+
+// builds the shared-memory tables for a given column placement; false when it does not fit
+inline bool build_cf_tables(const int32_t* bin_ptr, const int32_t* pos_feature, int f, int64_t ldb, int budget_bytes,
+                            CfHostTables* out) {
+  const int W = (f + 3) / 4;
+  if ((int64_t)W * 4 > ldb) return false;
+  const int nb = (W + 31) / 32;
+  if (nb > kCfMaxBlocks) return false;
+  CfLayout& L = out->lay;
+  memset(&L, 0, sizeof L);
+  L.n_blocks = nb;
+  int bank_rows[32] = {0};
+  struct Rec { int k, l, j, rowbase, feat; };
+  std::vector<Rec> recs;
+  for (int k = 0; k < nb; ++k) {
+    const int wk = std::min(32, W - 32 * k);
+    const int ck = 32 / wk;
+    L.wk[k] = wk; L.ck[k] = ck;
+    for (int l = 0; l < 32; ++l) {
+      L.skipword[k][l] = 0xFFFFFFFFu;
+      for (int j = 0; j < 4; ++j) L.a0[k][l][j] = -1;
+      if (l >= ck * wk) continue;
+      const int word = 32 * k + l % wk;
+      for (int j = 0; j < 4; ++j) {
+        const int feat = pos_feature[word * 4 + j];
+        if (feat < 0) continue;
+        if (feat >= f) return false;
+        const int nbins = bin_ptr[feat + 1] - bin_ptr[feat];
+        L.a0[k][l][j] = bank_rows[l] * 32 + l;
+        recs.push_back(Rec{k, l, j, bank_rows[l], feat});
+        bank_rows[l] += nbins;
+      }
+    }
+  }
+  int R = 1;
+  for (int l = 0; l < 32; ++l) R = std::max(R, bank_rows[l]);
+  L.R = R;
+  if ((int64_t)R * 32 * 8 > budget_bytes) return false;
+  out->slot_of.assign((size_t)R * 32, -1);
+  out->fold_src.clear(); out->fold_dst.clear();
+  for (const Rec& r : recs) {
+    const int wk = L.wk[r.k];
+    const int nbins = bin_ptr[r.feat + 1] - bin_ptr[r.feat];
+    if (r.l < wk) {
+      for (int b = 0; b < nbins; ++b) out->slot_of[(size_t)(r.rowbase + b) * 32 + r.l] = bin_ptr[r.feat] + b;
+    } else {
+      const int l0 = r.l % wk;
+      const int dst0 = L.a0[r.k][l0][r.j];
+      for (int b = 0; b < nbins; ++b) {
+        out->fold_src.push_back((r.rowbase + b) * 32 + r.l);
+        out->fold_dst.push_back(dst0 + b * 32);
+      }
+    }
+  }
+  L.n_fold = (int)out->fold_src.size();
+  // every feature must have been placed exactly once
+  std::vector<int> seen(f, 0);
+  for (int64_t p = 0; p < (int64_t)W * 4; ++p)
+    if (pos_feature[p] >= 0) seen[pos_feature[p]]++;
+  for (int i = 0; i < f; ++i)
+    if (seen[i] != 1) return false;
+  return true;
+}
+
+// 1024 threads = 32 warps; warp w takes row groups w, w + 32, ... of the CTA's slice.
+// Partials are written in shared-memory order ([2][R*32] int32), un-permuted by the reduce kernel.
+template <int UNROLL>
+__global__ void __launch_bounds__(1024, 1)
+hist_accum_cf_kernel(const uint32_t* __restrict__ bins32, int wpr, const int2* __restrict__ gpair,
+                     const uint32_t* __restrict__ row_idx, int identity, const HistPlan* __restrict__ plan,
+                     const CfLayout* __restrict__ lay, const int32_t* __restrict__ fold_src,
+                     const int32_t* __restrict__ fold_dst, int32_t* __restrict__ partials) {
+  extern __shared__ int32_t smem[];
+  const int slot = plan->cta_slot[blockIdx.x];
+  if (slot < 0) return;
+  const int RW = lay->R * 32;                 // words per array
+  int32_t* sG = smem;
+  int32_t* sH = smem + RW;
+  for (int s = threadIdx.x; s < 2 * RW; s += blockDim.x) smem[s] = 0;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nblk = lay->n_blocks, n_fold = lay->n_fold;
+  __syncthreads();
+  const int pos0 = plan->cta_begin[blockIdx.x];
+  const int rows = plan->cta_rows[blockIdx.x];
+  int pid = plan->cta_pbase[blockIdx.x];
+  for (int c0 = 0; c0 < rows; c0 += kChunkRows, ++pid) {
+    const int crow = min(kChunkRows, rows - c0);
+    for (int k = 0; k < nblk; ++k) {
+      const int wk = lay->wk[k], ck = lay->ck[k];
+      const bool active = lane < wk * ck;
+      const int rslot = lane / wk;
+      const int word = 32 * k + (lane - rslot * wk);
+      int a0[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) a0[j] = lay->a0[k][lane][j];
+      const uint32_t skipw = lay->skipword[k][lane];
+      for (int g0 = warp; g0 * ck < crow; g0 += 32 * UNROLL) {
+        uint32_t wv[UNROLL];
+        int2 gp[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+          const int i = (g0 + 32 * u) * ck + rslot;
+          const bool ok = active && i < crow;
+          wv[u] = skipw;                                  // every byte equal to its skip code: nothing added
+          gp[u] = make_int2(0, 0);
+          if (ok) {
+            const int pos = pos0 + c0 + i;
+            const uint32_t r = identity ? (uint32_t)pos : __ldg(row_idx + pos);
+            wv[u] = __ldg(bins32 + (size_t)r * wpr + word);
+            gp[u] = __ldg(gpair + r);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+          const uint32_t eq = __vcmpeq4(wv[u], skipw);     // 0xff in the bytes that are skipped
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (!((eq >> (8 * j)) & 1u) && a0[j] >= 0) {
+              const int a = a0[j] + (int)((wv[u] >> (8 * j)) & 255u) * 32;
+              atomicAdd(sG + a, gp[u].x);
+              atomicAdd(sH + a, gp[u].y);
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < n_fold; e += blockDim.x) {   // fold row-slot copies into copy 0
+      const int s = __ldg(fold_src + e), d = __ldg(fold_dst + e);
+      const int g = sG[s], h = sH[s];
+      if (g) atomicAdd(sG + d, g);
+      if (h) atomicAdd(sH + d, h);
+    }
+    __syncthreads();
+    int32_t* pp = partials + (size_t)pid * 2 * RW;
+    for (int s = threadIdx.x; s < 2 * RW; s += blockDim.x) {
+      pp[s] = smem[s];
+      smem[s] = 0;
+    }
+    __syncthreads();
+  }
+}
+
+// level buffer [slot][S][2] int64 += sum over a z-slice of the node's partials, un-permuted through
+// slot_of.  The level buffer must be zero before the launch (atomic adds from the z-slices).
+__global__ void __launch_bounds__(256) hist_reduce_cf_kernel(const int32_t* __restrict__ partials,
+                                                             const HistPlan* __restrict__ plan, int R, int S,
+                                                             const int32_t* __restrict__ slot_of,
+                                                             int64_t* __restrict__ level_buf) {
+  __shared__ long long tg[32][33], th[32][33];
+  const int j = blockIdx.y;
+  if (j >= plan->n_build) return;
+  const int p0 = plan->b_pbeg[j], p1 = plan->b_pbeg[j + 1];
+  const int np = p1 - p0, nz = gridDim.z;
+  const int per = (np + nz - 1) / nz;
+  const int pa = p0 + blockIdx.z * per, pb = min(p1, pa + per);
+  if (pa >= pb) return;
+  const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+  const int r0 = blockIdx.x * 32;
+  const size_t RW = (size_t)R * 32;
+  long long g[4] = {0, 0, 0, 0}, h[4] = {0, 0, 0, 0};
+  for (int p = pa; p < pb; ++p) {
+    const int32_t* pp = partials + (size_t)p * 2 * RW;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = r0 + wq * 4 + i;
+      if (r < R) {
+        g[i] += __ldg(pp + (size_t)r * 32 + lane);
+        h[i] += __ldg(pp + RW + (size_t)r * 32 + lane);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { tg[wq * 4 + i][lane] = g[i]; th[wq * 4 + i][lane] = h[i]; }
+  __syncthreads();
+  unsigned long long* out = reinterpret_cast<unsigned long long*>(level_buf) + (size_t)j * 2 * S;
+  for (int it = 0; it < 4; ++it) {
+    const int bank = wq * 4 + it, rr = lane, r = r0 + rr;      // consecutive lanes -> consecutive bins of one bank
+    if (r < R) {
+      const int s = __ldg(slot_of + (size_t)r * 32 + bank);
+      if (s >= 0) {
+        const long long a = tg[rr][bank], b = th[rr][bank];
+        if (a) atomicAdd(out + 2 * (size_t)s, (unsigned long long)a);
+        if (b) atomicAdd(out + 2 * (size_t)s + 1, (unsigned long long)b);
+      }
+    }
+  }
+}
+
+__global__ void zero_i64_kernel(int64_t* p, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = 0;
+}
+
+}  // namespace cb

@@ -20,6 +20,7 @@ __device__ __forceinline__ uint32_t bin_of(float x, const float* __restrict__ c,
 __global__ void __launch_bounds__(256) bin_pack_kernel(const float* __restrict__ X, int64_t n, int f, int64_t ldx,
                                                        const float* __restrict__ cuts,
                                                        const int32_t* __restrict__ n_cuts,
+                                                       const int32_t* __restrict__ pos_feature,
                                                        uint32_t* __restrict__ bins32, int wpr) {
   int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (item >= n * wpr) return;
@@ -29,9 +30,9 @@ __global__ void __launch_bounds__(256) bin_pack_kernel(const float* __restrict__
   uint32_t out = 0;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    int feat = 4 * w + j;
+    int feat = pos_feature ? __ldg(pos_feature + 4 * w + j) : (4 * w + j < f ? 4 * w + j : -1);
     uint32_t code = CB_MISSING_BIN;
-    if (feat < f) code = bin_of(__ldg(x + feat), cuts + (size_t)feat * CB_CUT_STRIDE, __ldg(n_cuts + feat));
+    if (feat >= 0) code = bin_of(__ldg(x + feat), cuts + (size_t)feat * CB_CUT_STRIDE, __ldg(n_cuts + feat));
     out |= code << (8 * j);
   }
   bins32[item] = out;
@@ -128,7 +129,7 @@ __device__ inline void plan_ctas(HistPlan* plan, int n_build, const int* begins,
   int spare = grid - n_build, b = 0, p = 0;
   for (int j = 0; j < n_build; ++j) {
     int nj = 1 + (total > 0 ? (int)((long long)spare * counts[j] / total) : 0);
-    int need = (counts[j] + kChunkRows - 1) / kChunkRows;   // no more CTAs than chunks
+    int need = (counts[j] + 255) / 256;                     // at least 256 rows per CTA
     nj = max(1, min(nj, need));
     int per = (counts[j] + nj - 1) / nj;
     per = (per + 31) & ~31;

@@ -100,7 +100,8 @@ __global__ void __launch_bounds__(256) level_finish_kernel(TreeState* st, int le
                                                            const FeatBest* __restrict__ feat_best, int f,
                                                            const float* __restrict__ cuts,
                                                            const float* __restrict__ min_vals, cb_tree_params p,
-                                                           NodeArrays na, TreeOut to, LevelSegs* segs) {
+                                                           NodeArrays na, TreeOut to, LevelSegs* segs,
+                                                           const int32_t* __restrict__ feat_pos) {
   __shared__ float s_chg[kMaxLevelNodes];
   __shared__ int s_feat[kMaxLevelNodes];
   __shared__ int s_child[kMaxLevelNodes];
@@ -172,7 +173,7 @@ __global__ void __launch_bounds__(256) level_finish_kernel(TreeState* st, int le
     const float bwR = __double2float_rn(calc_weight(__dmul_rn((double)GR, ig), __dmul_rn((double)HR, ih), p));
     to.sum_hess[L] = __double2float_rn(__dmul_rn((double)HL, ih));
     to.sum_hess[R] = __double2float_rn(__dmul_rn((double)HR, ih));
-    segs->feat[i] = bf; segs->bin[i] = fb.split_bin; segs->dl[i] = fb.default_left; segs->child[i] = L;
+    segs->feat[i] = feat_pos[bf]; segs->bin[i] = fb.split_bin; segs->dl[i] = fb.default_left; segs->child[i] = L;
     if (level + 1 == max_depth) {
       const float lL = __fmul_rn(bwL, p.eta), lR = __fmul_rn(bwR, p.eta);
       to.split_cond[L] = lL; to.base_weight[L] = lL;

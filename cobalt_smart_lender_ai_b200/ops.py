@@ -79,14 +79,30 @@ def bin_ptr_of(n_cuts: torch.Tensor) -> torch.Tensor:
     return bp
 
 
-def bin_pack(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, ldb: int | None = None) -> torch.Tensor:
-    """K2.  Returns u8 [n, ldb]."""
-    _need_cuda(X, cuts, n_cuts)
+def plan_layout(n_cuts, n_features: int, ldb: int | None = None):
+    """Column placement of the binned matrix (host computation inside the library).
+    Returns (pos_feature int32 [ldb] on the host, conflict_free flag)."""
+    import numpy as np
+    nc = np.ascontiguousarray(n_cuts.cpu().numpy() if isinstance(n_cuts, torch.Tensor) else n_cuts, dtype=np.int32)
+    ldb = ldb or padded_ldb(n_features)
+    pos = np.empty(ldb, np.int32)
+    flag = C.c_int32(0)
+    check(_lib.load().cb_plan_layout(nc.ctypes.data_as(C.c_void_p), n_features, ldb, pos.ctypes.data_as(C.c_void_p),
+                                     C.byref(flag)))
+    return pos, bool(flag.value)
+
+
+def bin_pack(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, ldb: int | None = None,
+             pos_feature: torch.Tensor | None = None) -> torch.Tensor:
+    """K2.  Returns u8 [n, ldb]; byte p of a row holds feature pos_feature[p] (natural order when None)."""
+    _need_cuda(X, cuts, n_cuts, pos_feature)
     assert X.dtype == torch.float32 and X.stride(1) == 1
     n, f = X.shape
     ldb = ldb or padded_ldb(f)
+    assert pos_feature is None or (pos_feature.dtype == torch.int32 and pos_feature.numel() == ldb)
     bins = torch.empty((n, ldb), dtype=torch.uint8, device=X.device)
-    check(_lib.load().cb_bin_pack_u8(_ptr(X), n, f, X.stride(0), _ptr(cuts), _ptr(n_cuts), _ptr(bins), ldb, _stream()))
+    check(_lib.load().cb_bin_pack_u8(_ptr(X), n, f, X.stride(0), _ptr(cuts), _ptr(n_cuts), _ptr(pos_feature),
+                                     _ptr(bins), ldb, _stream()))
     return bins
 
 

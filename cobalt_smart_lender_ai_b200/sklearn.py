@@ -169,7 +169,9 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
             base_score = float(self.base_score) if self.base_score is not None else estimate_base_score(pos_w, neg_w)
             sg, sh = ops.quant_shifts(max(1.0, spw) * wmax_s)
             cuts, n_cuts, min_vals = parallel.sketch_cuts_global(Xd, int(self.max_bin))
-            bins = ops.bin_pack(Xd, cuts, n_cuts)
+            pos_np, _cf = ops.plan_layout(n_cuts, f)
+            pos = torch.from_numpy(pos_np).to(dev)
+            bins = ops.bin_pack(Xd, cuts, n_cuts, pos_feature=pos)
             del Xd
             bin_ptr = ops.bin_ptr_of(n_cuts)
             T = int(self.n_estimators)
@@ -181,7 +183,7 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
                             reg_alpha=float(self.reg_alpha), gamma=float(self.gamma),
                             min_child_weight=float(self.min_child_weight), scale_pos_weight=spw, sg=sg, sh=sh,
                             subsample=float(self.subsample), seed=seed, max_trees=max(T, 1),
-                            base_margin=base_margin_of(base_score), row_offset=row_offset)
+                            base_margin=base_margin_of(base_score), row_offset=row_offset, pos_feature=pos)
             tr.boost(T, masks_d)
             forest = tr.forest_numpy()
             self._gpu_launches = tr.launch_count()

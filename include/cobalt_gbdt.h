@@ -31,7 +31,7 @@ extern "C" {
 #define CB_MISSING_BIN 255 /* u8 code of a missing value (R2) */
 #define CB_MAX_BINS 255    /* real bins per feature (R2) */
 #define CB_CUT_STRIDE 256  /* cuts are stored [n_features][256], padded with +inf */
-#define CB_QBITS 18        /* |q_g| <= 2^18 per row (R4); equals oracle.QBITS */
+#define CB_QBITS 17        /* |q_g| <= 2^17 per row (R4); equals oracle.QBITS */
 
 typedef enum {
   CB_OK = 0,
@@ -54,10 +54,19 @@ int cb_sketch_workspace_bytes(int64_t n_rows, int n_features, size_t* bytes);
 int cb_sketch_cuts(const float* X, int64_t n_rows, int n_features, int64_t ldx, int max_bin, float* cuts,
                    int32_t* n_cuts, float* min_vals, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- column placement of the binned matrix (HOST arrays, no device work).
+ * pos_feature_host[p] = feature stored in byte p of a binned row, -1 = padding.  Features are
+ * dealt to u32 words by descending bin count so that the histogram kernel can give every lane
+ * its own shared-memory bank; *conflict_free = 0 means the layout did not fit and the natural
+ * order (tiled kernel) is returned.  No reference counterpart (layout is internal to xgboost). */
+int cb_plan_layout(const int32_t* n_cuts_host, int n_features, int64_t ldb, int32_t* pos_feature_host,
+                   int32_t* conflict_free);
+
 /* ---- K2 bin-index packing (R2): bins u8 row major [n][ldb], ldb % 4 == 0, pad = 255.
+ * pos_feature: i32 [ldb] (device) from cb_plan_layout, or NULL for the natural order.
  * Replaces xgboost's GHistIndexMatrix build inside fit (same call sites as K1). */
 int cb_bin_pack_u8(const float* X, int64_t n_rows, int n_features, int64_t ldx, const float* cuts,
-                   const int32_t* n_cuts, uint8_t* bins, int64_t ldb, void* stream);
+                   const int32_t* n_cuts, const int32_t* pos_feature, uint8_t* bins, int64_t ldb, void* stream);
 
 /* ---- K3 logistic gradient/hessian in fixed point (R4).
  * Replaces the binary:logistic objective with scale_pos_weight
@@ -146,6 +155,7 @@ typedef struct {
   const int32_t* bin_ptr;  /* [f+1] */
   const float* cuts;       /* [f][256] */
   const float* min_vals;   /* [f] */
+  const int32_t* pos_feature; /* [ldb] column placement used when the rows were binned, or NULL */
   /* forest out, each [max_trees][max_nodes], max_nodes = 2^(max_depth+1)-1 (wire format a-9) */
   int32_t* left; int32_t* right; int32_t* parent; int32_t* split_index; int32_t* split_bin;
   float* split_cond; uint8_t* default_left; float* base_weight; float* loss_chg; float* sum_hess;

@@ -18,7 +18,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "liboracle.so")
-QBITS = 18  # |q_g| <= 2^QBITS per row (R4); must equal the product's CB_QBITS
+QBITS = 17  # |q_g| <= 2^QBITS per row (R4); must equal the product's CB_QBITS
 
 
 def build(force: bool = False) -> str:
