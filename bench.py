@@ -147,13 +147,13 @@ def run_ours(args):
         cuts, n_cuts, min_vals = parallel.sketch_cuts_global(X, 256)
         pos_np, cf_flag = ops.plan_layout(n_cuts, N_FEAT)
         pos = torch.from_numpy(pos_np).to(dev)
-        bins = ops.bin_pack(X, cuts, n_cuts, pos_feature=pos)
+        bins = ops.bin_pack(X, cuts, n_cuts, pos_feature=pos, blocked=cf_flag)
     t_prep = _timed(prep, world, dev)
     bin_ptr = ops.bin_ptr_of(n_cuts)
     S = int(bin_ptr[-1].item())
     total_rounds = args.warmup + args.steps + 4
     tr = GpuTrainer(bins, y, None, N_FEAT, bin_ptr, cuts, min_vals, max_depth=DEPTH, eta=ETA, scale_pos_weight=spw,
-                    sg=sg, sh=sh, max_trees=total_rounds, row_offset=r0, pos_feature=pos)
+                    sg=sg, sh=sh, max_trees=total_rounds, row_offset=r0, pos_feature=pos, blocked=cf_flag)
     tr.boost(args.warmup)
     l0 = tr.launch_count()
     with ClockSampler(dev.index or 0) as clk:
@@ -199,6 +199,14 @@ def run_ours(args):
     bins_cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         bp_ = bins.cpu().numpy()
+        if cf_flag and bp_.shape[1] > 128:                      # block-major -> row-major
+            n_, ldb_ = bp_.shape
+            flat, parts, off = bp_.reshape(-1), [], 0
+            for k0 in range(0, ldb_, 128):
+                w_ = min(128, ldb_ - k0)
+                parts.append(flat[off: off + n_ * w_].reshape(n_, w_))
+                off += n_ * w_
+            bp_ = np.concatenate(parts, axis=1)
         bins_cpu = np.full_like(bp_, 255)
         placed = pos_np >= 0
         bins_cpu[:, pos_np[placed]] = bp_[:, placed]       # back to the natural column order the oracle reads

@@ -42,7 +42,7 @@ class TrainConfig(C.Structure):
     _fields_ = [("n_rows", C.c_int64), ("ldb", C.c_int64), ("row_offset", C.c_int64), ("n_features", C.c_int32),
                 ("total_bins", C.c_int32), ("max_trees", C.c_int32), ("world_size", C.c_int32),
                 ("tree", TreeParams), ("scale_pos_weight", C.c_float), ("keep_thresh", C.c_uint32),
-                ("seed", C.c_uint32), ("pad_", C.c_int32)]
+                ("seed", C.c_uint32), ("blocked", C.c_int32)]
 
 
 class TrainBuffers(C.Structure):
@@ -85,7 +85,7 @@ _SIGS = {
     "cb_sketch_workspace_bytes": (C.c_int, [_I64, _I, C.POINTER(_SZ)]),
     "cb_sketch_cuts": (C.c_int, [_VP, _I64, _I, _I64, _I, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "cb_plan_layout": (C.c_int, [_VP, _I, _I64, _VP, C.POINTER(C.c_int32)]),
-    "cb_bin_pack_u8": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _VP, _VP, _I64, _VP]),
+    "cb_bin_pack_u8": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _VP, _VP, _I64, _I, _VP]),
     "cb_grad_logistic_q": (C.c_int, [_VP, _VP, _VP, _I64, _F, _I, _I, _U32, _U32, _U32, _I64, _VP, _VP, _VP]),
     "cb_sigmoid": (C.c_int, [_VP, _I64, _VP, _VP]),
     "cb_hist_workspace_bytes": (C.c_int, [_I64, _I, C.POINTER(_SZ)]),

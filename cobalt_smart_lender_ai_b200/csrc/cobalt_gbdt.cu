@@ -91,14 +91,14 @@ int cb_plan_layout(const int32_t* n_cuts_host, int f, int64_t ldb, int32_t* pos_
 }
 
 int cb_bin_pack_u8(const float* X, int64_t n, int f, int64_t ldx, const float* cuts, const int32_t* n_cuts,
-                   const int32_t* pos_feature, uint8_t* bins, int64_t ldb, void* stream) {
+                   const int32_t* pos_feature, uint8_t* bins, int64_t ldb, int blocked, void* stream) {
   if (!X || !cuts || !n_cuts || !bins || n < 0 || f <= 0 || ldx < f || ldb < f || (ldb & 3))
     return fail(CB_ERR_INVALID, "cb_bin_pack_u8: bad arguments (ldb must be a multiple of 4 and >= n_features)");
   if (n == 0) return CB_OK;
   int wpr = (int)(ldb / 4);
   int64_t items = n * wpr;
-  bin_pack_kernel<<<ceil_div(items, 256), 256, 0, (cudaStream_t)stream>>>(X, n, f, ldx, cuts, n_cuts, pos_feature,
-                                                                         reinterpret_cast<uint32_t*>(bins), wpr);
+  bin_pack_kernel<<<ceil_div(items, 256), 256, 0, (cudaStream_t)stream>>>(X, n, f, ldx, cuts, n_cuts, pos_feature, bins, wpr,
+                                                                         make_view(bins, n, ldb, blocked));
   CB_LAUNCH_CHECK();
   return CB_OK;
 }
@@ -275,7 +275,7 @@ int cb_partition_stable(const uint8_t* bins, int64_t ldb, const uint32_t* seg_in
   uint32_t* flag_bits = b.take<uint32_t>((size_t)(count / 32 + 2));
   int* tile_cnt = b.take<int>((size_t)(count / kPartTile + 2));
   const int nt = ceil_div(count, kPartTile);
-  part1_flags_kernel<<<nt, 256, 0, s>>>(bins, ldb, seg_in, count, feature, split_bin, default_left, flag_bits, tile_cnt);
+  part1_flags_kernel<<<nt, 256, 0, s>>>(make_view(bins, 0, ldb, 0), seg_in, count, feature, split_bin, default_left, flag_bits, tile_cnt);
   part2_scan_kernel<<<1, 1024, 0, s>>>(tile_cnt, nt, n_left);
   part3_scatter_kernel<<<nt, 256, 0, s>>>(seg_in, count, flag_bits, tile_cnt, n_left, seg_out);
   CB_LAUNCH_CHECK();
@@ -455,6 +455,9 @@ int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, v
       if (fp[i] < 0) { delete t; return fail(CB_ERR_INVALID, "trainer: pos_feature does not place feature %d", i); }
     CfHostTables tb;
     t->cf = build_cf_tables(bp.data(), pf.data(), f, cfg->ldb, budget * 8, &tb);
+    const bool multi = (cfg->ldb + 127) / 128 > 1;
+    if (t->cf && multi && !cfg->blocked) t->cf = false;     // row-major rows wider than one block: tiled kernel
+    if (!t->cf && multi && cfg->blocked) { delete t; return fail(CB_ERR_UNSUPPORTED, "trainer: block-major bins need a conflict-free layout"); }
     e = cudaMemcpy(t->feat_pos, fp.data(), sizeof(int32_t) * f, cudaMemcpyHostToDevice);
     if (t->cf && e == cudaSuccess) {
       t->cf_R = tb.lay.R; t->cf_smem = tb.lay.R * 32 * 8;
@@ -464,7 +467,8 @@ int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, v
         e = cudaMemcpy(t->cf_fold_src, tb.fold_src.data(), sizeof(int32_t) * tb.fold_src.size(), cudaMemcpyHostToDevice);
         if (e == cudaSuccess) e = cudaMemcpy(t->cf_fold_dst, tb.fold_dst.data(), sizeof(int32_t) * tb.fold_dst.size(), cudaMemcpyHostToDevice);
       }
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(hist_accum_cf_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, t->cf_smem);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(hist_accum_cf_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCfSmemBytes);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(hist_accum_cf_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCfSmemBytes);
     }
     if (e != cudaSuccess) { delete t; return fail(CB_ERR_CUDA, "cb_trainer_create: %s", cudaGetErrorString(e)); }
   }
@@ -539,9 +543,15 @@ int cb_trainer_level_hist(cb_trainer* t, int level, void* stream) {
   if (t->cf) {
     CB_CUDA(cudaMemsetAsync(t->level_buf, 0, sizeof(int64_t) * (size_t)nb * t->S2, s));
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
-    hist_accum_cf_kernel<4><<<t->grid, 1024, t->cf_smem, s>>>(
-        reinterpret_cast<const uint32_t*>(t->buf.bins), (int)(t->cfg.ldb / 4), t->gpair, t->rows[t->cur],
-        t->identity ? 1 : 0, t->plan, t->cf_lay, t->cf_fold_src, t->cf_fold_dst, t->partials);
+    const BinsView bv = make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked);
+    if (t->identity)
+      hist_accum_cf_kernel<4, true><<<t->grid, 1024, kCfSmemBytes, s>>>(
+          t->buf.bins, bv.blocked ? t->cfg.n_rows : 0, bv.blocked ? bv.last_w : (int)t->cfg.ldb, t->gpair,
+          t->rows[t->cur], t->plan, t->cf_lay, t->cf_fold_src, t->cf_fold_dst, t->partials);
+    else
+      hist_accum_cf_kernel<4, false><<<t->grid, 1024, kCfSmemBytes, s>>>(
+          t->buf.bins, bv.blocked ? t->cfg.n_rows : 0, bv.blocked ? bv.last_w : (int)t->cfg.ldb, t->gpair,
+          t->rows[t->cur], t->plan, t->cf_lay, t->cf_fold_src, t->cf_fold_dst, t->partials);
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[1], s));
     const int tiles = ceil_div(t->cf_R, 32);
     int nz = (2 * t->di.sm_count) / (tiles * nb);
@@ -594,7 +604,7 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   const int ident = t->identity ? 1 : 0;
   if (level + 1 < D) {
     uint32_t* rout = t->rows[t->cur ^ 1];
-    part_level_flags_kernel<<<t->n_part_tiles, 256, 0, s>>>(t->buf.bins, t->cfg.ldb, rin, ident, n, t->segs,
+    part_level_flags_kernel<<<t->n_part_tiles, 256, 0, s>>>(make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked), rin, ident, n, t->segs,
                                                             t->flag_bits, t->tile_cnt);
     part_level_scan_kernel<<<1, 1024, 0, s>>>(t->tile_cnt, t->n_part_tiles, n, t->flag_bits, t->segs, t->st, level, D,
                                               t->na, t->plan, t->grid, t->cfg.world_size > 1 ? 1 : 0);
@@ -603,7 +613,7 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
     t->cur ^= 1; t->identity = false;
     t->launches += 3;
   } else {
-    final_apply_kernel<<<ceil_div(n, 256), 256, 0, s>>>(t->buf.bins, t->cfg.ldb, rin, ident, n, t->segs, t->buf.margin);
+    final_apply_kernel<<<ceil_div(n, 256), 256, 0, s>>>(make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked), rin, ident, n, t->segs, t->buf.margin);
     t->launches += 1;
   }
   CB_LAUNCH_CHECK();

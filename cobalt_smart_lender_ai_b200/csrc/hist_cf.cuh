@@ -29,7 +29,7 @@ struct CfLayout {                      // device copy lives in the trainer works
   int wk[kCfMaxBlocks];                // words in the block
   int ck[kCfMaxBlocks];                // rows per warp instruction (= private copies)
   int a0[kCfMaxBlocks][32][4];         // word index of bin 0 of the byte's feature, -1 = padding byte
-  uint32_t skipword[kCfMaxBlocks][32]; // per byte: the code that is NOT accumulated (255 = missing)
+  int nbj[kCfMaxBlocks][32][4];        // bins of the byte's feature: codes are clamped to it, row nbj = missing/dump
 };
 
 struct CfHostTables {
@@ -75,8 +75,7 @@ inline bool build_cf_tables(const int32_t* bin_ptr, const int32_t* pos_feature, 
     const int ck = 32 / wk;
     L.wk[k] = wk; L.ck[k] = ck;
     for (int l = 0; l < 32; ++l) {
-      L.skipword[k][l] = 0xFFFFFFFFu;
-      for (int j = 0; j < 4; ++j) L.a0[k][l][j] = -1;
+      for (int j = 0; j < 4; ++j) { L.a0[k][l][j] = -1; L.nbj[k][l][j] = 0; }
       if (l >= ck * wk) continue;
       const int word = 32 * k + l % wk;
       for (int j = 0; j < 4; ++j) {
@@ -85,15 +84,21 @@ inline bool build_cf_tables(const int32_t* bin_ptr, const int32_t* pos_feature, 
         if (feat >= f) return false;
         const int nbins = bin_ptr[feat + 1] - bin_ptr[feat];
         L.a0[k][l][j] = bank_rows[l] * 32 + l;
+        L.nbj[k][l][j] = nbins;
         recs.push_back(Rec{k, l, j, bank_rows[l], feat});
-        bank_rows[l] += nbins;
+        bank_rows[l] += nbins + 1;                      // + the row that takes missing values
       }
     }
   }
   int R = 1;
   for (int l = 0; l < 32; ++l) R = std::max(R, bank_rows[l]);
+  R += 1;                                               // last row: dump slot of padding bytes
   L.R = R;
-  if ((int64_t)R * 32 * 8 > budget_bytes) return false;
+  for (int k = 0; k < nb; ++k)
+    for (int l = 0; l < 32; ++l)
+      for (int j = 0; j < 4; ++j)
+        if (L.a0[k][l][j] < 0) { L.a0[k][l][j] = (R - 1) * 32 + l; L.nbj[k][l][j] = 0; }
+  if (R > 896 || (int64_t)2 * 28672 * 4 > budget_bytes + 2048) return false;   // kCfMaxRows, kCfSmemBytes
   out->slot_of.assign((size_t)R * 32, -1);
   out->fold_src.clear(); out->fold_dst.clear();
   for (const Rec& r : recs) {
@@ -120,23 +125,54 @@ inline bool build_cf_tables(const int32_t* bin_ptr, const int32_t* pos_feature, 
   return true;
 }
 
-// 1024 threads = 32 warps; warp w takes row groups w, w + 32, ... of the CTA's slice.
+constexpr int kCfHOffWords = 28672;            // H array at a fixed +112 KB: an immediate in the ATOMS address
+constexpr int kCfMaxRows = kCfHOffWords / 32;  // 896 rows of 32 banks per array
+constexpr int kCfSmemBytes = 2 * kCfHOffWords * 4;
+
+__device__ __forceinline__ uint32_t ldg_nc_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+
+// one byte of a bin word: clamp the code to the feature's bin count (255 = missing lands in the
+// row after the last bin, which the reduce kernel ignores) and add (g, h) in the lane's own bank.
+// 5 issue slots per byte: PRMT, VIMNMX, IMAD, 2 x ATOMS; no predicates, no branches.
+template <int POS>
+__device__ __forceinline__ void cf_add_byte_at(uint32_t word, uint32_t nb, uint32_t base, int g, int h) {
+  asm volatile(
+      "{\n\t"
+      ".reg .u32 b, a;\n\t"
+      "bfe.u32 b, %0, %1, 8;\n\t"
+      "min.u32 b, b, %2;\n\t"
+      "mad.lo.u32 a, b, 128, %3;\n\t"
+      "red.shared.add.s32 [a], %4;\n\t"
+      "red.shared.add.s32 [a+114688], %5;\n\t"
+      "}\n"
+      :
+      : "r"(word), "n"(POS), "r"(nb), "r"(base), "r"(g), "r"(h)
+      : "memory");
+}
+
+// 1024 threads = 32 warps; warp w takes row groups w, w + 32, ... of the CTA's slice, one column
+// block after the other (each block is its own contiguous array: block-major storage).
 // Partials are written in shared-memory order ([2][R*32] int32), un-permuted by the reduce kernel.
-template <int UNROLL>
+template <int UNROLL, bool IDENTITY>
 __global__ void __launch_bounds__(1024, 1)
-hist_accum_cf_kernel(const uint32_t* __restrict__ bins32, int wpr, const int2* __restrict__ gpair,
-                     const uint32_t* __restrict__ row_idx, int identity, const HistPlan* __restrict__ plan,
+hist_accum_cf_kernel(const uint8_t* __restrict__ bins, int64_t n_rows, int last_w, const int2* __restrict__ gpair,
+                     const uint32_t* __restrict__ row_idx, const HistPlan* __restrict__ plan,
                      const CfLayout* __restrict__ lay, const int32_t* __restrict__ fold_src,
                      const int32_t* __restrict__ fold_dst, int32_t* __restrict__ partials) {
   extern __shared__ int32_t smem[];
   const int slot = plan->cta_slot[blockIdx.x];
   if (slot < 0) return;
-  const int RW = lay->R * 32;                 // words per array
+  const int RW = lay->R * 32;                 // used words per array
   int32_t* sG = smem;
-  int32_t* sH = smem + RW;
-  for (int s = threadIdx.x; s < 2 * RW; s += blockDim.x) smem[s] = 0;
+  int32_t* sH = smem + kCfHOffWords;
+  for (int s = threadIdx.x; s < RW; s += blockDim.x) { sG[s] = 0; sH[s] = 0; }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nblk = lay->n_blocks, n_fold = lay->n_fold;
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
   __syncthreads();
   const int pos0 = plan->cta_begin[blockIdx.x];
   const int rows = plan->cta_rows[blockIdx.x];
@@ -146,39 +182,35 @@ hist_accum_cf_kernel(const uint32_t* __restrict__ bins32, int wpr, const int2* _
     for (int k = 0; k < nblk; ++k) {
       const int wk = lay->wk[k], ck = lay->ck[k];
       const bool active = lane < wk * ck;
-      const int rslot = lane / wk;
-      const int word = 32 * k + (lane - rslot * wk);
-      int a0[4];
+      const int rslot = active ? lane / wk : 0;
+      const int wl = active ? lane - rslot * wk : 0;
+      const int bw = (k == nblk - 1) ? last_w : 128;                 // bytes per row of this block
+      const uint8_t* bbase = bins + (size_t)n_rows * 128 * k + 4 * wl;
+      uint32_t base[4], nbj[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) a0[j] = lay->a0[k][lane][j];
-      const uint32_t skipw = lay->skipword[k][lane];
+      for (int j = 0; j < 4; ++j) {
+        base[j] = sbase + 4u * (uint32_t)lay->a0[k][lane][j];
+        nbj[j] = (uint32_t)lay->nbj[k][lane][j];
+      }
+      const int ilast = crow - 1;
       for (int g0 = warp; g0 * ck < crow; g0 += 32 * UNROLL) {
         uint32_t wv[UNROLL];
         int2 gp[UNROLL];
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) {
           const int i = (g0 + 32 * u) * ck + rslot;
-          const bool ok = active && i < crow;
-          wv[u] = skipw;                                  // every byte equal to its skip code: nothing added
-          gp[u] = make_int2(0, 0);
-          if (ok) {
-            const int pos = pos0 + c0 + i;
-            const uint32_t r = identity ? (uint32_t)pos : __ldg(row_idx + pos);
-            wv[u] = __ldg(bins32 + (size_t)r * wpr + word);
-            gp[u] = __ldg(gpair + r);
-          }
+          const int pos = pos0 + c0 + min(i, ilast);                 // clamped: always a valid row, no branch
+          const uint32_t r = IDENTITY ? (uint32_t)pos : __ldg(row_idx + pos);
+          wv[u] = ldg_nc_u32(reinterpret_cast<const uint32_t*>(bbase + (size_t)r * bw));
+          gp[u] = __ldg(gpair + r);
+          if (!active || i > ilast) gp[u] = make_int2(0, 0);         // adds zero: harmless
         }
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) {
-          const uint32_t eq = __vcmpeq4(wv[u], skipw);     // 0xff in the bytes that are skipped
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            if (!((eq >> (8 * j)) & 1u) && a0[j] >= 0) {
-              const int a = a0[j] + (int)((wv[u] >> (8 * j)) & 255u) * 32;
-              atomicAdd(sG + a, gp[u].x);
-              atomicAdd(sH + a, gp[u].y);
-            }
-          }
+          cf_add_byte_at<0>(wv[u], nbj[0], base[0], gp[u].x, gp[u].y);
+          cf_add_byte_at<8>(wv[u], nbj[1], base[1], gp[u].x, gp[u].y);
+          cf_add_byte_at<16>(wv[u], nbj[2], base[2], gp[u].x, gp[u].y);
+          cf_add_byte_at<24>(wv[u], nbj[3], base[3], gp[u].x, gp[u].y);
         }
       }
     }
@@ -191,9 +223,9 @@ hist_accum_cf_kernel(const uint32_t* __restrict__ bins32, int wpr, const int2* _
     }
     __syncthreads();
     int32_t* pp = partials + (size_t)pid * 2 * RW;
-    for (int s = threadIdx.x; s < 2 * RW; s += blockDim.x) {
-      pp[s] = smem[s];
-      smem[s] = 0;
+    for (int s = threadIdx.x; s < RW; s += blockDim.x) {
+      pp[s] = sG[s]; pp[RW + s] = sH[s];
+      sG[s] = 0; sH[s] = 0;
     }
     __syncthreads();
   }

@@ -17,11 +17,34 @@ __device__ __forceinline__ uint32_t bin_of(float x, const float* __restrict__ c,
   return (uint32_t)(lo == nc ? nc - 1 : lo);
 }
 
+// Where the byte of column position p of a row lives.  Row major: base[row * ldb + p].
+// Block major (conflict-free layout): column block k = p / 128 is its own [n_rows][width_k] array,
+// width 128 except for the last block, so every block is read as whole aligned lines.
+struct BinsView {
+  const uint8_t* base;
+  int64_t n_rows, ldb;
+  int blocked, n_blocks, last_w;
+};
+__host__ __device__ inline BinsView make_view(const uint8_t* base, int64_t n_rows, int64_t ldb, int blocked) {
+  BinsView v;
+  v.base = base; v.n_rows = n_rows; v.ldb = ldb; v.blocked = blocked;
+  v.n_blocks = (int)((ldb + 127) / 128);
+  v.last_w = (int)(ldb - 128 * (int64_t)(v.n_blocks - 1));
+  if (v.n_blocks <= 1) v.blocked = 0;
+  return v;
+}
+__device__ __forceinline__ size_t byte_index(const BinsView& v, int64_t row, int p) {
+  if (!v.blocked) return (size_t)row * v.ldb + p;
+  const int k = p >> 7;
+  const int w = (k == v.n_blocks - 1) ? v.last_w : 128;
+  return (size_t)v.n_rows * 128 * k + (size_t)row * w + (p & 127);
+}
+
 __global__ void __launch_bounds__(256) bin_pack_kernel(const float* __restrict__ X, int64_t n, int f, int64_t ldx,
                                                        const float* __restrict__ cuts,
                                                        const int32_t* __restrict__ n_cuts,
                                                        const int32_t* __restrict__ pos_feature,
-                                                       uint32_t* __restrict__ bins32, int wpr) {
+                                                       uint8_t* __restrict__ bins, int wpr, BinsView view) {
   int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (item >= n * wpr) return;
   int64_t row = item / wpr;
@@ -35,7 +58,7 @@ __global__ void __launch_bounds__(256) bin_pack_kernel(const float* __restrict__
     if (feat >= 0) code = bin_of(__ldg(x + feat), cuts + (size_t)feat * CB_CUT_STRIDE, __ldg(n_cuts + feat));
     out |= code << (8 * j);
   }
-  bins32[item] = out;
+  *reinterpret_cast<uint32_t*>(bins + byte_index(view, row, 4 * w)) = out;
 }
 
 // =====================================================================================
@@ -355,13 +378,12 @@ __device__ __forceinline__ FeatBest scan_feature(const int64_t* __restrict__ his
 // =====================================================================================
 // K6  stable partition, standalone single-segment form (the trainer has the level-wide form)
 // =====================================================================================
-__device__ __forceinline__ bool goes_left(const uint8_t* __restrict__ bins, int64_t ldb, uint32_t row, int feat,
-                                          int split_bin, int default_left) {
-  int c = __ldg(bins + (size_t)row * ldb + feat);
+__device__ __forceinline__ bool goes_left(const BinsView& v, uint32_t row, int pos, int split_bin, int default_left) {
+  int c = __ldg(v.base + byte_index(v, row, pos));
   return c == CB_MISSING_BIN ? default_left != 0 : c <= split_bin;
 }
 
-__global__ void __launch_bounds__(256) part1_flags_kernel(const uint8_t* __restrict__ bins, int64_t ldb,
+__global__ void __launch_bounds__(256) part1_flags_kernel(BinsView view,
                                                           const uint32_t* __restrict__ seg, int64_t count, int feat,
                                                           int split_bin, int default_left,
                                                           uint32_t* __restrict__ flag_bits, int* __restrict__ tile_cnt) {
@@ -372,7 +394,7 @@ __global__ void __launch_bounds__(256) part1_flags_kernel(const uint8_t* __restr
   for (int it = 0; it < kPartTile / 256; ++it) {
     int64_t pos = tile0 + (int64_t)wid * (kPartTile / 8) + it * 32 + lane;
     bool fl = false;
-    if (pos < count) fl = goes_left(bins, ldb, seg[pos], feat, split_bin, default_left);
+    if (pos < count) fl = goes_left(view, seg[pos], feat, split_bin, default_left);
     uint32_t bal = __ballot_sync(0xffffffffu, fl);
     if (lane == 0 && pos < count) flag_bits[pos >> 5] = bal;
     cnt += __popc(bal);

@@ -204,7 +204,7 @@ struct SegCache {
 };
 
 // P1: go-left flags of every position that sits in a node being split (kind 1)
-__global__ void __launch_bounds__(256) part_level_flags_kernel(const uint8_t* __restrict__ bins, int64_t ldb,
+__global__ void __launch_bounds__(256) part_level_flags_kernel(BinsView view,
                                                                const uint32_t* __restrict__ rows_in, int identity,
                                                                int n_rows, const LevelSegs* __restrict__ segs,
                                                                uint32_t* __restrict__ flag_bits,
@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(256) part_level_flags_kernel(const uint8_t* __
       const int i = find_seg(sc.begin, sc.count, n, pos);
       if (i >= 0 && segs->kind[i] == 1) {
         const uint32_t row = identity ? (uint32_t)pos : __ldg(rows_in + pos);
-        fl = goes_left(bins, ldb, row, segs->feat[i], segs->bin[i], segs->dl[i]);
+        fl = goes_left(view, row, segs->feat[i], segs->bin[i], segs->dl[i]);
       }
     }
     const uint32_t bal = __ballot_sync(0xffffffffu, fl);
@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(256) part_level_scatter_kernel(const uint32_t*
 }
 
 // last level: children are leaves, so rows are not moved; each row takes its child's leaf value
-__global__ void __launch_bounds__(256) final_apply_kernel(const uint8_t* __restrict__ bins, int64_t ldb,
+__global__ void __launch_bounds__(256) final_apply_kernel(BinsView view,
                                                           const uint32_t* __restrict__ rows_in, int identity,
                                                           int n_rows, const LevelSegs* __restrict__ segs,
                                                           float* __restrict__ margin) {
@@ -372,7 +372,7 @@ __global__ void __launch_bounds__(256) final_apply_kernel(const uint8_t* __restr
   if (i < 0) return;
   const uint32_t row = identity ? (uint32_t)pos : __ldg(rows_in + pos);
   float leaf = segs->leafL[i];
-  if (segs->kind[i] == 2 && !goes_left(bins, ldb, row, segs->feat[i], segs->bin[i], segs->dl[i])) leaf = segs->leafR[i];
+  if (segs->kind[i] == 2 && !goes_left(view, row, segs->feat[i], segs->bin[i], segs->dl[i])) leaf = segs->leafR[i];
   margin[row] = __fadd_rn(margin[row], leaf);
 }
 

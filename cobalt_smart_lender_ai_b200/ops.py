@@ -93,8 +93,10 @@ def plan_layout(n_cuts, n_features: int, ldb: int | None = None):
 
 
 def bin_pack(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, ldb: int | None = None,
-             pos_feature: torch.Tensor | None = None) -> torch.Tensor:
-    """K2.  Returns u8 [n, ldb]; byte p of a row holds feature pos_feature[p] (natural order when None)."""
+             pos_feature: torch.Tensor | None = None, blocked: bool = False) -> torch.Tensor:
+    """K2.  Returns n * ldb bytes as a u8 [n, ldb] tensor; byte p of a row holds feature pos_feature[p]
+    (natural order when None).  blocked=True stores column blocks of 128 bytes as separate arrays
+    (see cb_bin_pack_u8) -- the tensor shape then only carries n and ldb."""
     _need_cuda(X, cuts, n_cuts, pos_feature)
     assert X.dtype == torch.float32 and X.stride(1) == 1
     n, f = X.shape
@@ -102,7 +104,7 @@ def bin_pack(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, ldb: int
     assert pos_feature is None or (pos_feature.dtype == torch.int32 and pos_feature.numel() == ldb)
     bins = torch.empty((n, ldb), dtype=torch.uint8, device=X.device)
     check(_lib.load().cb_bin_pack_u8(_ptr(X), n, f, X.stride(0), _ptr(cuts), _ptr(n_cuts), _ptr(pos_feature),
-                                     _ptr(bins), ldb, _stream()))
+                                     _ptr(bins), ldb, int(bool(blocked)), _stream()))
     return bins
 
 

@@ -171,7 +171,7 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
             cuts, n_cuts, min_vals = parallel.sketch_cuts_global(Xd, int(self.max_bin))
             pos_np, _cf = ops.plan_layout(n_cuts, f)
             pos = torch.from_numpy(pos_np).to(dev)
-            bins = ops.bin_pack(Xd, cuts, n_cuts, pos_feature=pos)
+            bins = ops.bin_pack(Xd, cuts, n_cuts, pos_feature=pos, blocked=_cf)
             del Xd
             bin_ptr = ops.bin_ptr_of(n_cuts)
             T = int(self.n_estimators)
@@ -183,7 +183,7 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
                             reg_alpha=float(self.reg_alpha), gamma=float(self.gamma),
                             min_child_weight=float(self.min_child_weight), scale_pos_weight=spw, sg=sg, sh=sh,
                             subsample=float(self.subsample), seed=seed, max_trees=max(T, 1),
-                            base_margin=base_margin_of(base_score), row_offset=row_offset, pos_feature=pos)
+                            base_margin=base_margin_of(base_score), row_offset=row_offset, pos_feature=pos, blocked=_cf)
             tr.boost(T, masks_d)
             forest = tr.forest_numpy()
             self._gpu_launches = tr.launch_count()

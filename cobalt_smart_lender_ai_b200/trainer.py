@@ -29,7 +29,7 @@ class GpuTrainer:
                  eta: float = 0.3, reg_lambda: float = 1.0, reg_alpha: float = 0.0, gamma: float = 0.0,
                  min_child_weight: float = 1.0, scale_pos_weight: float = 1.0, sg: int, sh: int,
                  subsample: float = 1.0, seed: int = 0, max_trees: int = 100, base_margin: float = 0.0,
-                 row_offset: int = 0, group=None, pos_feature: torch.Tensor | None = None):
+                 row_offset: int = 0, group=None, pos_feature: torch.Tensor | None = None, blocked: bool = False):
         if not bins.is_cuda:
             raise _lib.CobaltError("GpuTrainer needs CUDA tensors: this package has no CPU path")
         self.lib = _lib.load()
@@ -52,7 +52,8 @@ class GpuTrainer:
         tp = TreeParams(float(np.float32(eta)), float(reg_lambda), float(reg_alpha), float(gamma),
                         float(min_child_weight), int(max_depth), int(sg), int(sh))
         self.cfg = TrainConfig(n, ldb, int(row_offset), n_features, total_bins, max_trees, self.world, tp,
-                               float(scale_pos_weight), ops.keep_threshold(subsample), int(seed) & 0xFFFFFFFF, 0)
+                               float(scale_pos_weight), ops.keep_threshold(subsample), int(seed) & 0xFFFFFFFF,
+                               int(bool(blocked)))
         need = C.c_size_t()
         check(self.lib.cb_trainer_workspace_bytes(C.byref(self.cfg), C.byref(need)))
         self.ws = ops.workspace(need.value, self.dev)

@@ -62,11 +62,15 @@ int cb_sketch_cuts(const float* X, int64_t n_rows, int n_features, int64_t ldx, 
 int cb_plan_layout(const int32_t* n_cuts_host, int n_features, int64_t ldb, int32_t* pos_feature_host,
                    int32_t* conflict_free);
 
-/* ---- K2 bin-index packing (R2): bins u8 row major [n][ldb], ldb % 4 == 0, pad = 255.
+/* ---- K2 bin-index packing (R2): bins u8, n * ldb bytes, ldb % 4 == 0, pad = 255.
  * pos_feature: i32 [ldb] (device) from cb_plan_layout, or NULL for the natural order.
+ * blocked = 0: row major [n][ldb].  blocked = 1: column-block major -- bytes [128k, 128k+128) of
+ * every row form their own [n][width_k] array at byte offset n * 128 * k (width 128, last block
+ * ldb - 128k), so each block streams as whole aligned lines (what the conflict-free histogram reads).
  * Replaces xgboost's GHistIndexMatrix build inside fit (same call sites as K1). */
 int cb_bin_pack_u8(const float* X, int64_t n_rows, int n_features, int64_t ldx, const float* cuts,
-                   const int32_t* n_cuts, const int32_t* pos_feature, uint8_t* bins, int64_t ldb, void* stream);
+                   const int32_t* n_cuts, const int32_t* pos_feature, uint8_t* bins, int64_t ldb, int blocked,
+                   void* stream);
 
 /* ---- K3 logistic gradient/hessian in fixed point (R4).
  * Replaces the binary:logistic objective with scale_pos_weight
@@ -144,11 +148,11 @@ typedef struct {
   float scale_pos_weight;
   uint32_t keep_thresh;
   uint32_t seed;
-  int32_t pad_;
+  int32_t blocked;    /* storage of `bins`: 0 row major, 1 column-block major (see cb_bin_pack_u8) */
 } cb_train_config;
 
 typedef struct {
-  const uint8_t* bins;     /* [n][ldb] */
+  const uint8_t* bins;     /* n * ldb bytes, layout per cb_train_config.blocked */
   const uint8_t* y;        /* [n] */
   const float* weight;     /* [n] or NULL */
   float* margin;           /* [n] in/out */

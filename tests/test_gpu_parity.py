@@ -89,6 +89,8 @@ def test_bin_pack_bit_exact(ops, data):
         placed = pos >= 0
         assert sorted(pos[placed].tolist()) == list(range(X.shape[1]))
         assert np.array_equal(got[:, placed], want[:, pos[placed]]) and np.all(got[:, ~placed] == 255)
+        got_b = ops.bin_pack(_dev(X), _dev(cuts), _dev(nc), ldb, _dev(pos), blocked=True).cpu().numpy()
+        assert np.array_equal(got_b, _block_major(got))
 
 
 def test_sigmoid_and_grad_bit_exact(ops):
@@ -222,24 +224,31 @@ def test_partition_stable_bit_exact(ops, data, cnt):
         assert np.array_equal(got.cpu().numpy().view(np.uint32), want)
 
 
+def _block_major(b):
+    """[n][ldb] row-major -> the library's column-block-major storage (same shape, different byte order)."""
+    n, ldb = b.shape
+    parts = [np.ascontiguousarray(b[:, k:k + 128]).reshape(-1) for k in range(0, ldb, 128)]
+    return np.concatenate(parts).reshape(n, ldb)
+
+
 def _train_gpu(ops, ref, X, y, n_trees, spw, subsample=1.0, seed=0, masks=None, weight=None, natural=False, **kw):
     from cobalt_smart_lender_ai_b200.trainer import GpuTrainer
     tp = ref["tp"]
-    pos = None
+    pos, _cf = None, False
     if natural:
         bins = _dev(ref["bins"])
     else:  # the product's column placement applied to the oracle's bins
-        pos_np, _ = ops.plan_layout(ref["n_cuts"], X.shape[1], ref["bins"].shape[1])
+        pos_np, _cf = ops.plan_layout(ref["n_cuts"], X.shape[1], ref["bins"].shape[1])
         b = np.full_like(ref["bins"], 255)
         placed = pos_np >= 0
         b[:, placed] = ref["bins"][:, pos_np[placed]]
-        bins, pos = _dev(b), _dev(pos_np)
+        bins, pos = _dev(_block_major(b) if _cf else b), _dev(pos_np)
     tr = GpuTrainer(bins, _dev(y), None if weight is None else _dev(weight), X.shape[1], _dev(ref["bin_ptr"]),
                     _dev(ref["cuts"]), _dev(ref["min_vals"]), max_depth=tp.max_depth, eta=tp.eta,
                     reg_lambda=tp.reg_lambda, reg_alpha=tp.reg_alpha, gamma=tp.gamma,
                     min_child_weight=tp.min_child_weight, scale_pos_weight=spw, sg=tp.sg, sh=tp.sh,
                     subsample=subsample, seed=seed, max_trees=n_trees, base_margin=O.base_margin_of(ref["base_score"]),
-                    group=False, pos_feature=pos)
+                    group=False, pos_feature=pos, blocked=_cf)
     tr.boost(n_trees, None if masks is None else _dev(masks))
     return tr
 
@@ -336,6 +345,21 @@ def test_train_natural_order_and_tiled_fallback(ops, data):
     assert np.array_equal(tr.margin.cpu().numpy().view(np.uint32), ref["margin"].view(np.uint32))
 
 
+def test_train_150_features_two_column_blocks(ops):
+    """The BASELINE schema (150 columns -> two column blocks, row-slot copies folded, block-major storage)."""
+    from cobalt_smart_lender_ai_b200.synth import make_lending
+    X, y, _ = make_lending(30000, 150, seed=5)
+    X, y = X.numpy(), y.numpy()
+    spw = float((y == 0).sum() / (y == 1).sum())
+    ref = O.fit_reference(X, y, n_estimators=4, max_depth=6, scale_pos_weight=spw, want_rows=True, want_hist=True)
+    assert ops.plan_layout(ref["n_cuts"], 150)[1]
+    tr = _train_gpu(ops, ref, X, y, 4, spw)
+    _assert_forest_equal(tr.forest_numpy(), ref["flat"])
+    assert np.array_equal(tr.margin.cpu().numpy().view(np.uint32), ref["margin"].view(np.uint32))
+    assert np.array_equal(tr.node_hist(0).cpu().numpy(), ref["forest"]["root_hist"])
+    assert np.array_equal(_final_rows(ref, tr, ref["bins"]), ref["forest"]["row_order"])
+
+
 def test_train_colsample_and_weights(ops, data):
     from cobalt_smart_lender_ai_b200.sklearn import colsample_masks
     X, y, _ = data
@@ -424,12 +448,12 @@ def test_full_size_properties(ops):
     pos_np, cf = ops.plan_layout(n_cuts, f)
     assert cf
     pos = torch.from_numpy(pos_np).cuda()
-    bins = ops.bin_pack(X, cuts, n_cuts, pos_feature=pos)
+    bins = ops.bin_pack(X, cuts, n_cuts, pos_feature=pos, blocked=True)
     bp = ops.bin_ptr_of(n_cuts)
     spw = float(((y == 0).sum() / (y == 1).sum()).item())
     sg, sh = ops.quant_shifts(spw)
     tr = GpuTrainer(bins, y, None, f, bp, cuts, min_vals, max_depth=6, eta=0.3, scale_pos_weight=spw, sg=sg, sh=sh,
-                    max_trees=3, group=False, pos_feature=pos)
+                    max_trees=3, group=False, pos_feature=pos, blocked=True)
     tr.boost(3)
     fo = tr.forest_numpy()
     a = int(fo["tree_offsets"][2])
