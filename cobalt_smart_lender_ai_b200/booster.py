@@ -40,6 +40,51 @@ def pack_forest(tree_offsets, left, right, split_index, split_cond, default_left
     return nodes.view(np.int64), np.asarray(tree_offsets, np.int32)
 
 
+def heap_forest(tree_offsets, left, right, split_index, split_cond, default_left, max_depth_cap: int = 10):
+    """Wire-format forest -> complete trees in heap order (cb_predict_heap).  Where a branch ends
+    above the common depth the leaf is carried down through pass-through nodes whose two children
+    are the same.  Returns (thr f32 [T,NI], meta u16 [T,NI], leaf f32 [T,NL], depth) or None when
+    a tree is deeper than max_depth_cap."""
+    offs = np.asarray(tree_offsets, np.int64)
+    T = len(offs) - 1
+    left = np.asarray(left, np.int64)
+    right = np.asarray(right, np.int64)
+    feat = np.asarray(split_index, np.int64)
+    cond = np.asarray(split_cond, np.float32)
+    dl = np.asarray(default_left, np.int64)
+    if T == 0:
+        return None
+    cur = offs[:-1].copy()[:, None]                      # [T, nodes at this level] absolute node ids
+    levels = []
+    depth = 0
+    while True:
+        internal = left[cur] >= 0
+        if not internal.any():
+            break
+        if depth >= max_depth_cap:
+            return None
+        levels.append((cur, internal))
+        base = np.repeat(offs[:-1][:, None], cur.shape[1], axis=1)
+        lch = np.where(internal, base + left[cur], cur)
+        rch = np.where(internal, base + right[cur], cur)
+        cur = np.stack([lch, rch], axis=2).reshape(T, -1)
+        depth += 1
+    if depth == 0:                                       # forest of single-leaf trees: one pass-through level
+        levels.append((cur, np.zeros_like(cur, bool)))
+        cur = np.concatenate([cur, cur], axis=1)
+        depth = 1
+    NI = (1 << depth) - 1
+    thr = np.zeros((T, NI), np.float32)
+    meta = np.zeros((T, NI), np.uint16)
+    pos = 0
+    for ids, internal in levels:
+        w = ids.shape[1]
+        thr[:, pos:pos + w] = np.where(internal, cond[ids], np.float32(0.0))
+        meta[:, pos:pos + w] = np.where(internal, feat[ids] | (dl[ids] << 15), 0).astype(np.uint16)
+        pos += w
+    return thr, meta, np.ascontiguousarray(cond[cur]), depth
+
+
 class Booster:
     def __init__(self, forest: dict, n_features: int, feature_names=None, base_score: float = 0.5,
                  attributes: dict | None = None):
@@ -104,7 +149,37 @@ class Booster:
         """X: CUDA f32 [n, n_features].  Returns p (or the margin) as a CUDA f32 [n] tensor."""
         if X.shape[1] != self.n_features:
             raise ValueError(f"Feature shape mismatch, expected: {self.n_features}, got {X.shape[1]}")
-        nodes, toff = self._device_forest(X.device)
-        m, p = ops.predict(X, nodes, toff, base_margin_of(self.base_score), want_margin=output_margin,
-                           want_proba=not output_margin)
+        heap = self._device_heap(X.device)
+        if heap is not None:
+            nodes_h, leaf, depth = heap
+            m, p = ops.predict_heap(X, nodes_h, leaf, depth, base_margin_of(self.base_score),
+                                    self.num_boosted_rounds(), want_margin=output_margin, want_proba=not output_margin)
+        else:                                            # very deep trees: pointer-chasing kernel
+            nodes, toff = self._device_forest(X.device)
+            m, p = ops.predict(X, nodes, toff, base_margin_of(self.base_score), want_margin=output_margin,
+                               want_proba=not output_margin)
         return m if output_margin else p
+
+    def _device_heap(self, device):
+        key = "heap:" + str(device)
+        if key not in self._dev_cache:
+            fo = self.forest
+            h = heap_forest(fo["tree_offsets"], fo["left"], fo["right"], fo["split_index"], fo["split_cond"],
+                            fo["default_left"])
+            if h is not None and self.n_features > 32767:
+                h = None
+            chunk, rows = ops.predict_heap_plan(self.n_features, h[3]) if h is not None else (0, 0)
+            if h is None or chunk < 8:
+                self._dev_cache[key] = None
+            else:
+                thr, meta, leaf, depth = h
+                T = thr.shape[0]
+                Tp = (T + chunk - 1) // chunk * chunk
+                xoff = (meta.astype(np.uint64) & np.uint64(0x7FFF)) * np.uint64(rows * 4)
+                hi = xoff | ((meta.astype(np.uint64) >> np.uint64(15)) << np.uint64(31))
+                nodes = thr.view(np.uint32).astype(np.uint64) | (hi << np.uint64(32))
+                pad = lambda a: np.concatenate([a, np.zeros((Tp - T,) + a.shape[1:], a.dtype)], 0)  # noqa: E731
+                with torch.cuda.device(device):
+                    self._dev_cache[key] = (torch.from_numpy(pad(nodes).view(np.int64)).to(device),
+                                            torch.from_numpy(pad(leaf)).to(device), depth)
+        return self._dev_cache[key]

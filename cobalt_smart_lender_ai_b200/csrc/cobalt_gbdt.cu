@@ -1,4 +1,5 @@
 // libcobalt_gbdt.so -- C ABI over the sm_100a kernels (see include/cobalt_gbdt.h).
+#include <cstdlib>
 #include <new>
 
 #include "sketch.cuh"
@@ -301,6 +302,69 @@ int cb_predict(const float* X, int64_t n, int f, int64_t ldx, const uint64_t* no
   }
   predict_kernel<<<ceil_div(n, kPredRows), kPredRows, smem, (cudaStream_t)stream>>>(
       X, n, f, ldx, reinterpret_cast<const uint2*>(nodes), tree_off, n_trees, base_margin, out_margin, out_proba);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+// trees per shared-memory chunk for the complete-tree scorer: two buffers next to the row tile
+static int heap_chunk_trees(const DeviceInfo& di, int f, int depth, int* rows_out) {
+  const int NI = (1 << depth) - 1, NL = 1 << depth;
+  const int per_tree = NI * 8 + NL * 4;
+  int rows = 256;
+  for (;;) {
+    const int64_t tile = (((int64_t)f * rows * 4 + 127) & ~(int64_t)127);
+    const int64_t avail = (int64_t)di.smem_optin - tile - 1280;
+    int chunk = avail > 0 ? (int)(avail / 2 / per_tree) & ~7 : 0;
+    if (chunk >= 8 || rows <= 32) {
+      *rows_out = rows;
+      return chunk > 512 ? 512 : chunk;
+    }
+    rows >>= 1;
+  }
+}
+
+int cb_predict_heap_plan(int n_features, int depth, int* chunk_trees, int* tile_rows) {
+  if (!chunk_trees || !tile_rows || n_features <= 0 || depth < 1 || depth > 12) return fail(CB_ERR_INVALID, "cb_predict_heap_plan: bad arguments");
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  int rows = 0;
+  *chunk_trees = heap_chunk_trees(di, n_features, depth, &rows);
+  *tile_rows = rows;
+  if (*chunk_trees < 8) return fail(CB_ERR_UNSUPPORTED, "cb_predict_heap: %d features at depth %d do not fit shared memory", n_features, depth);
+  return CB_OK;
+}
+
+int cb_predict_heap(const float* X, int64_t n, int f, int64_t ldx, const uint64_t* nodes, const float* leaf,
+                    int n_trees, int depth, float base_margin, float* out_margin, float* out_proba, void* stream) {
+  if (n == 0) return CB_OK;
+  if (!X || !nodes || !leaf || n < 0 || f <= 0 || f > 32767 || ldx < f || n_trees < 0 || depth < 1 || depth > 12 ||
+      (!out_margin && !out_proba))
+    return fail(CB_ERR_INVALID, "cb_predict_heap: bad arguments");
+  if ((reinterpret_cast<uintptr_t>(nodes) | reinterpret_cast<uintptr_t>(leaf)) & 15)
+    return fail(CB_ERR_INVALID, "cb_predict_heap: forest arrays must be 16-byte aligned");
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  int rows = 0;
+  const int chunk = heap_chunk_trees(di, f, depth, &rows);
+  if (chunk < 8) return fail(CB_ERR_UNSUPPORTED, "cb_predict_heap: %d features at depth %d do not fit shared memory", f, depth);
+  const int NI = (1 << depth) - 1, NL = 1 << depth;
+  const int64_t tile = (((int64_t)f * rows * 4 + 127) & ~(int64_t)127);
+  const int smem = (int)(tile + 2 * (int64_t)chunk * (NI * 8 + NL * 4) + 128);
+  static thread_local int attr_dev = -1;
+  if (attr_dev != di.device) {
+    CB_CUDA(cudaFuncSetAttribute(predict_heap_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, di.smem_optin - 1024));
+    CB_CUDA(cudaFuncSetAttribute(predict_heap_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, di.smem_optin - 1024));
+    attr_dev = di.device;
+  }
+  const char* ilp_env = getenv("COBALT_PRED_ILP");
+  if (ilp_env && atoi(ilp_env) == 4)
+    predict_heap_kernel<4><<<ceil_div(n, rows), rows, smem, (cudaStream_t)stream>>>(
+        X, n, f, ldx, reinterpret_cast<const uint2*>(nodes), leaf, n_trees, depth, chunk, base_margin, out_margin, out_proba);
+  else
+    predict_heap_kernel<8><<<ceil_div(n, rows), rows, smem, (cudaStream_t)stream>>>(
+        X, n, f, ldx, reinterpret_cast<const uint2*>(nodes), leaf, n_trees, depth, chunk, base_margin, out_margin, out_proba);
   CB_LAUNCH_CHECK();
   return CB_OK;
 }

@@ -506,4 +506,139 @@ __global__ void __launch_bounds__(kPredRows) predict_kernel(const float* __restr
   if (out_proba) out_proba[row0 + r] = spec_sigmoid(m);
 }
 
+// ---- K8, complete-tree form: every tree is padded to a complete binary tree of depth D in heap
+// order (node i -> children 2i+1, 2i+2; pass-through nodes where a branch ended early), so the
+// nodes of one level are contiguous: a warp's 32 lanes read <= 32 consecutive threshold words
+// -> one shared-memory wavefront, no child pointers.  Tree chunks are staged in shared memory
+// next to the feature-major row tile; every thread walks 4 trees at a time (independent
+// dependency chains) and adds the 4 leaves in tree order, so the f32 sum equals the oracle's.
+// --- minimal mbarrier / 1-D bulk-copy (TMA) wrappers: one thread streams the next tree chunk
+// from L2 into shared memory while the CTA walks the current one.
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(bar);
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "W_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@!p bra W_%=;\n\t}\n" ::"r"(a),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   (uint32_t)__cvta_generic_to_shared(dst)),
+               "l"(src), "r"(bytes), "r"((uint32_t)__cvta_generic_to_shared(bar))
+               : "memory");
+}
+
+// nodes: [Tp][NI] uint2 {threshold bits, byte offset of the feature's row in the tile | default_left << 31}
+template <int ILP>
+__global__ void __launch_bounds__(256) predict_heap_kernel(const float* __restrict__ X, int64_t n, int f, int64_t ldx,
+                                                           const uint2* __restrict__ nodes,    // [Tp][NI]
+                                                           const float* __restrict__ leaf,     // [Tp][NL]
+                                                           int n_trees, int depth, int chunk_trees, float base_margin,
+                                                           float* __restrict__ out_margin, float* __restrict__ out_proba) {
+  extern __shared__ __align__(128) float xs[];  // [f][R] row tile, then two tree-chunk buffers
+  __shared__ __align__(8) uint64_t bars[2];
+  const int R = blockDim.x;
+  const int NI = (1 << depth) - 1, NL = 1 << depth;
+  const uint32_t node_b = (uint32_t)chunk_trees * NI * 8, leaf_b = (uint32_t)chunk_trees * NL * 4;  // chunk % 2 == 0
+  const uint32_t buf_b = node_b + leaf_b;
+  char* buf0 = reinterpret_cast<char*>(xs) + (((size_t)f * R * 4 + 127) & ~(size_t)127);
+  const int n_chunks = (n_trees + chunk_trees - 1) / chunk_trees;   // arrays are padded to whole chunks
+  if (threadIdx.x == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  auto issue = [&](int c) {
+    char* dst = buf0 + (size_t)(c & 1) * buf_b;
+    uint64_t* bar = &bars[c & 1];
+    mbar_expect_tx(bar, buf_b);
+    bulk_g2s(dst, nodes + (size_t)c * chunk_trees * NI, node_b, bar);
+    bulk_g2s(dst + node_b, leaf + (size_t)c * chunk_trees * NL, leaf_b, bar);
+  };
+  if (threadIdx.x == 0) {
+    issue(0);
+    if (n_chunks > 1) issue(1);
+  }
+  const int64_t row0 = (int64_t)blockIdx.x * R;
+  const int nrow = (int)min((int64_t)R, n - row0);
+  if (ldx == f) {
+    const float* src = X + row0 * ldx;
+    for (int i = threadIdx.x; i < nrow * f; i += R) {
+      int r = i / f, c = i - r * f;
+      xs[c * R + r] = __ldg(src + i);
+    }
+  } else {
+    for (int i = threadIdx.x; i < nrow * f; i += R) {
+      int r = i / f, c = i - r * f;
+      xs[c * R + r] = __ldg(X + (row0 + r) * ldx + c);
+    }
+  }
+  __syncthreads();
+  const int r = threadIdx.x;
+  const char* xr = reinterpret_cast<const char*>(xs + r);
+  float m = base_margin;
+  for (int c = 0; c < n_chunks; ++c) {
+    const char* buf = buf0 + (size_t)(c & 1) * buf_b;
+    const uint2* s_node = reinterpret_cast<const uint2*>(buf);
+    const float* s_leaf = reinterpret_cast<const float*>(buf + node_b);
+    mbar_wait(&bars[c & 1], (uint32_t)((c >> 1) & 1));
+    const int ct = min(chunk_trees, n_trees - c * chunk_trees);
+    if (r < nrow) {
+      int t = 0;
+      for (; t + ILP <= ct; t += ILP) {
+        int idx[ILP];
+        const uint2* tn[ILP];
+#pragma unroll
+        for (int k = 0; k < ILP; ++k) { idx[k] = 0; tn[k] = s_node + (t + k) * NI; }
+        for (int d = 0; d < depth; ++d) {
+          uint2 q[ILP];
+          float v[ILP];
+#pragma unroll
+          for (int k = 0; k < ILP; ++k) q[k] = tn[k][idx[k]];
+#pragma unroll
+          for (int k = 0; k < ILP; ++k) v[k] = *reinterpret_cast<const float*>(xr + (q[k].y & 0x7FFFFFFFu));
+#pragma unroll
+          for (int k = 0; k < ILP; ++k) {
+            const bool left = (v[k] < __uint_as_float(q[k].x)) | (((int)q[k].y < 0) & (v[k] != v[k]));
+            idx[k] = 2 * idx[k] + (left ? 1 : 2);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < ILP; ++k) m = __fadd_rn(m, s_leaf[(t + k) * NL + idx[k] - NI]);
+      }
+      for (; t < ct; ++t) {
+        int i0 = 0;
+        for (int d = 0; d < depth; ++d) {
+          const uint2 q0 = s_node[t * NI + i0];
+          const float v0 = *reinterpret_cast<const float*>(xr + (q0.y & 0x7FFFFFFFu));
+          const bool l0 = (v0 < __uint_as_float(q0.x)) | (((int)q0.y < 0) & (v0 != v0));
+          i0 = 2 * i0 + (l0 ? 1 : 2);
+        }
+        m = __fadd_rn(m, s_leaf[t * NL + i0 - NI]);
+      }
+    }
+    __syncthreads();                               // every thread is done with this buffer
+    if (threadIdx.x == 0 && c + 2 < n_chunks) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      issue(c + 2);
+    }
+  }
+  if (r < nrow) {
+    if (out_margin) out_margin[row0 + r] = m;
+    if (out_proba) out_proba[row0 + r] = spec_sigmoid(m);
+  }
+}
+
 }  // namespace cb

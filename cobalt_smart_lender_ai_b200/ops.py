@@ -191,3 +191,23 @@ def predict(X: torch.Tensor, nodes: torch.Tensor, tree_off: torch.Tensor, base_m
     check(_lib.load().cb_predict(_ptr(X), n, f, X.stride(0), _ptr(nodes), _ptr(tree_off), tree_off.numel() - 1,
                                  float(base_margin), _ptr(m), _ptr(p), _stream()))
     return m, p
+
+
+def predict_heap_plan(n_features: int, depth: int) -> tuple[int, int]:
+    """(trees per shared-memory chunk, rows per CTA tile) of the complete-tree scorer; (0, 0) = does not fit."""
+    c, r = C.c_int(0), C.c_int(0)
+    rc = _lib.load().cb_predict_heap_plan(n_features, depth, C.byref(c), C.byref(r))
+    return (c.value, r.value) if rc == 0 else (0, 0)
+
+
+def predict_heap(X: torch.Tensor, nodes: torch.Tensor, leaf: torch.Tensor, depth: int, base_margin: float,
+                 n_trees: int, want_margin: bool = False, want_proba: bool = True):
+    """K8, complete-tree form.  nodes int64 [Tp, 2^d-1] (packed), leaf f32 [Tp, 2^d], padded to whole chunks."""
+    _need_cuda(X, nodes, leaf)
+    assert X.dtype == torch.float32 and X.stride(1) == 1
+    n, f = X.shape
+    m = torch.empty(n, dtype=torch.float32, device=X.device) if want_margin else None
+    p = torch.empty(n, dtype=torch.float32, device=X.device) if want_proba else None
+    check(_lib.load().cb_predict_heap(_ptr(X), n, f, X.stride(0), _ptr(nodes), _ptr(leaf), int(n_trees), depth,
+                                      float(base_margin), _ptr(m), _ptr(p), _stream()))
+    return m, p

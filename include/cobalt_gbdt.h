@@ -133,6 +133,17 @@ int cb_predict(const float* X, int64_t n_rows, int n_features, int64_t ldx, cons
                const int32_t* tree_off, int n_trees, float base_margin, float* out_margin, float* out_proba,
                void* stream);
 
+/* ---- K8, complete-tree form (the fast path for forests of bounded depth): every tree padded to a
+ * complete binary tree of `depth` levels in heap order (node i -> children 2i+1, 2i+2).
+ * cb_predict_heap_plan gives, for the current device, the trees per shared-memory chunk and the rows
+ * per CTA tile.  nodes: u64 [Tp][2^depth - 1] = threshold bits | (feature * tile_rows * 4 | default_left << 31) << 32;
+ * leaf: f32 [Tp][2^depth]; Tp = n_trees rounded up to whole chunks; both 16-byte aligned (chunks are
+ * streamed into shared memory with bulk copies).  Same call sites as cb_predict; bit-identical results. */
+int cb_predict_heap_plan(int n_features, int depth, int* chunk_trees, int* tile_rows);
+int cb_predict_heap(const float* X, int64_t n_rows, int n_features, int64_t ldx, const uint64_t* nodes,
+                    const float* leaf, int n_trees, int depth, float base_margin, float* out_margin,
+                    float* out_proba, void* stream);
+
 /* ---- fused trainer: one boosting round = K3 + per level (K4, K9, K5, K6) + K7, with every
  * split decision kept on the device (no host synchronisation inside a tree).
  * Replaces the body of XGBClassifier.fit's boosting loop. */

@@ -391,6 +391,10 @@ def test_predict_fixture_forest(ops, fixture_forest):
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
     p = b.predict_device(_dev(X)).cpu().numpy()
     assert np.max(np.abs(p - O.sigmoid(want))) <= 1e-5
+    # the pointer-chasing kernel (used for very deep trees) gives the same bits as the complete-tree kernel
+    nodes, toff = b._device_forest(torch.device("cuda"))
+    m2, _ = ops.predict(_dev(X), nodes, toff, 0.0, want_margin=True, want_proba=False)
+    assert np.array_equal(m2.cpu().numpy().view(np.uint32), want.view(np.uint32))
     # ragged: 0 rows and 1 row
     assert b.predict_device(_dev(X[:1])).shape == (1,)
     assert b.predict_device(_dev(X[:0])).shape == (0,)
