@@ -310,15 +310,21 @@ int cb_predict(const float* X, int64_t n, int f, int64_t ldx, const uint64_t* no
 static int heap_chunk_trees(const DeviceInfo& di, int f, int depth, int* rows_out) {
   const int NI = (1 << depth) - 1, NL = 1 << depth;
   const int per_tree = NI * 8 + NL * 4;
-  int rows = 256;
+  // two CTAs per SM (one stages its row tile while the other walks trees) when 128-row tiles fit
+  const char* env = getenv("COBALT_PRED_ROWS");
+  int rows = env ? atoi(env) : 128;
+  if (rows != 256 && rows != 128 && rows != 64 && rows != 32) rows = 128;
   for (;;) {
     const int64_t tile = (((int64_t)f * rows * 4 + 127) & ~(int64_t)127);
-    const int64_t avail = (int64_t)di.smem_optin - tile - 1280;
+    const int per_sm = rows <= 128 ? 2 : 1;
+    const int64_t avail = (int64_t)(di.smem_optin + 1024) / per_sm - tile - 1280 - (per_sm > 1 ? 1024 : 0);
     int chunk = avail > 0 ? (int)(avail / 2 / per_tree) & ~7 : 0;
     if (chunk >= 8 || rows <= 32) {
       *rows_out = rows;
       return chunk > 512 ? 512 : chunk;
     }
+    if (rows == 128) { rows = 256; continue; }      // 128 did not fit twice: one CTA per SM with 256 rows
+    if (rows == 256) { rows = 64; continue; }
     rows >>= 1;
   }
 }

@@ -587,7 +587,6 @@ __global__ void __launch_bounds__(256) predict_heap_kernel(const float* __restri
   }
   __syncthreads();
   const int r = threadIdx.x;
-  const char* xr = reinterpret_cast<const char*>(xs + r);
   float m = base_margin;
   for (int c = 0; c < n_chunks; ++c) {
     const char* buf = buf0 + (size_t)(c & 1) * buf_b;
@@ -596,35 +595,48 @@ __global__ void __launch_bounds__(256) predict_heap_kernel(const float* __restri
     mbar_wait(&bars[c & 1], (uint32_t)((c >> 1) & 1));
     const int ct = min(chunk_trees, n_trees - c * chunk_trees);
     if (r < nrow) {
+      // byte offsets inside the chunk buffer: node address a -> children at 2a + (8 - tb) (+8 for right)
+      const uint32_t r4 = (uint32_t)r * 4u;     // low bits of every feature-row offset are free (R * 4 <= 1024 | offsets)
       int t = 0;
       for (; t + ILP <= ct; t += ILP) {
-        int idx[ILP];
-        const uint2* tn[ILP];
+        uint32_t a[ILP], c1[ILP];
 #pragma unroll
-        for (int k = 0; k < ILP; ++k) { idx[k] = 0; tn[k] = s_node + (t + k) * NI; }
+        for (int k = 0; k < ILP; ++k) { a[k] = (uint32_t)(t + k) * NI * 8u; c1[k] = 16u - a[k]; }
         for (int d = 0; d < depth; ++d) {
           uint2 q[ILP];
           float v[ILP];
 #pragma unroll
-          for (int k = 0; k < ILP; ++k) q[k] = tn[k][idx[k]];
+          for (int k = 0; k < ILP; ++k) q[k] = *reinterpret_cast<const uint2*>(buf + a[k]);
 #pragma unroll
-          for (int k = 0; k < ILP; ++k) v[k] = *reinterpret_cast<const float*>(xr + (q[k].y & 0x7FFFFFFFu));
+          for (int k = 0; k < ILP; ++k)
+            v[k] = *reinterpret_cast<const float*>(reinterpret_cast<const char*>(xs) + ((q[k].y & 0x7FFFFFFFu) | r4));
 #pragma unroll
           for (int k = 0; k < ILP; ++k) {
-            const bool left = (v[k] < __uint_as_float(q[k].x)) | (((int)q[k].y < 0) & (v[k] != v[k]));
-            idx[k] = 2 * idx[k] + (left ? 1 : 2);
+            // left = (v < thr) | (default_left & isnan(v));  a = 2a + c1 (right child), minus 8 when left.
+            // Written with predicates: the ALU pipe issues at half rate and bounds this loop.
+            asm("{\n\t.reg .pred pd, pn, pl;\n\t"
+                "setp.lt.s32 pd, %2, 0;\n\t"
+                "setp.nan.and.f32 pn, %1, %1, pd;\n\t"
+                "setp.lt.or.f32 pl, %1, %3, pn;\n\t"
+                "mad.lo.u32 %0, %0, 2, %4;\n\t"
+                "@pl sub.u32 %0, %0, 8;\n\t}"
+                : "+r"(a[k])
+                : "f"(v[k]), "r"(q[k].y), "f"(__uint_as_float(q[k].x)), "r"(c1[k]));
           }
         }
 #pragma unroll
-        for (int k = 0; k < ILP; ++k) m = __fadd_rn(m, s_leaf[(t + k) * NL + idx[k] - NI]);
+        for (int k = 0; k < ILP; ++k) {
+          const uint32_t li = ((a[k] + c1[k] - 16u) >> 1) - (uint32_t)NI * 4u;   // (idx - NI) * 4
+          m = __fadd_rn(m, *reinterpret_cast<const float*>(buf + node_b + (uint32_t)(t + k) * NL * 4u + li));
+        }
       }
       for (; t < ct; ++t) {
         int i0 = 0;
         for (int d = 0; d < depth; ++d) {
           const uint2 q0 = s_node[t * NI + i0];
-          const float v0 = *reinterpret_cast<const float*>(xr + (q0.y & 0x7FFFFFFFu));
-          const bool l0 = (v0 < __uint_as_float(q0.x)) | (((int)q0.y < 0) & (v0 != v0));
-          i0 = 2 * i0 + (l0 ? 1 : 2);
+          const float v0 = *reinterpret_cast<const float*>(reinterpret_cast<const char*>(xs) + ((q0.y & 0x7FFFFFFFu) | r4));
+          const uint32_t l0 = (uint32_t)(v0 < __uint_as_float(q0.x)) | ((q0.y >> 31) & (uint32_t)(v0 != v0));
+          i0 = 2 * i0 + 2 - (int)l0;
         }
         m = __fadd_rn(m, s_leaf[t * NL + i0 - NI]);
       }
