@@ -481,3 +481,36 @@ def test_full_size_properties(ops):
     # the sorted-ness property of the stable partition: every leaf segment is ascending in row id
     rows = tr.row_order().cpu().numpy().view(np.uint32)
     assert np.array_equal(np.sort(rows), np.arange(n, dtype=np.uint32))
+
+
+def test_scoring_service_on_gpu(ops, fixture_forest, tmp_path):
+    """src/api path end to end: the reference's shipped forest served through the FastAPI mirror
+    (/predict_bulk_csv -> predict_proba_df -> cb_predict_heap), model written and re-read as a .ubj file."""
+    import pandas as pd
+    from fastapi.testclient import TestClient
+
+    from cobalt_smart_lender_ai_b200 import ubjson
+    from cobalt_smart_lender_ai_b200.api import cobalt_fast_api as api
+    from cobalt_smart_lender_ai_b200.booster import Booster
+    ff = fixture_forest
+    names = [str(s) for s in ff["feature_names"]]
+    path = tmp_path / "model.ubj"
+    ubjson.save_model(Booster(ff, 20, names, float(ff["base_score"])), str(path))
+    api.xgb_model = api.load_model(path)
+    rng = np.random.default_rng(3)
+    X = (rng.normal(size=(50, 20)) * 200 + 400).astype(np.float32)
+    X[:, 12:] = rng.integers(0, 2, (50, 8))
+    df = pd.DataFrame(X.astype(np.float64), columns=names)
+    want = O.sigmoid(O.predict_margin(X, ff["tree_offsets"], ff["left"], ff["right"], ff["split_index"],
+                                      ff["split_cond"], ff["default_left"], 0.0))
+    assert np.max(np.abs(api.predict_proba_df(df) - want)) <= 1e-5
+    client = TestClient(api.app)
+    r = client.post("/predict_bulk_csv", files={"file": ("x.csv", df.to_csv(index=False), "text/csv")})
+    assert r.status_code == 200
+    got = np.array([rec["prob_default"] for rec in r.json()["predictions"]])
+    assert np.max(np.abs(got - want)) <= 1e-5
+    row = {n: float(df.iloc[0][n]) for n in names}
+    r = client.post("/predict", json=row)
+    assert r.status_code == 200 and abs(r.json()["prob_default"] - want[0]) <= 1e-5
+    r = client.post("/feature_importance_bulk", json={"data": [row]})
+    assert r.json()["top_features"][0]["feature"] in names

@@ -1,0 +1,205 @@
+"""CPU suite: host-side logic of the product (no compute calls, no GPU)."""
+import ctypes as C
+import os
+import pickle
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    """The C-ABI library builds/loads without a GPU and exports everything include/*.h declares."""
+    from cobalt_smart_lender_ai_b200 import _lib
+    lib = _lib.load()
+    assert lib.cb_version() == 100
+    hdr = open(os.path.join(ROOT, "include", "cobalt_gbdt.h")).read()
+    declared = set(re.findall(r"^(?:int|void|int64_t|const char\*)\s+(cb_[a-z0-9_]+)\s*\(", hdr, flags=re.M))
+    assert declared, "no declarations found"
+    raw = C.CDLL(_lib.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(raw, name), f"{name} declared in the header but not exported"
+    assert declared <= set(_lib.EXPORTS) | {"cb_version"}, declared - set(_lib.EXPORTS)
+
+
+def test_no_cpu_fallback_fails_loudly():
+    import torch
+
+    from cobalt_smart_lender_ai_b200 import _lib
+    from cobalt_smart_lender_ai_b200.sklearn import XGBClassifier
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(_lib.CobaltError):
+        XGBClassifier().fit(np.zeros((4, 2), np.float32), np.array([0, 1, 0, 1]))
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "cobalt_smart_lender_ai_b200")
+    for dp, _, fns in os.walk(pkg):
+        for fn in fns:
+            if fn.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dp, fn)).read()
+                assert "oracle" not in src.replace("the oracle", "").replace("oracle's", "").replace("oracle.QBITS", "") \
+                    or "import oracle" not in src and "from oracle" not in src, fn
+                assert "from oracle" not in src and "import oracle" not in src, fn
+
+
+def test_estimator_contract_clone_params_pickle():
+    from sklearn.base import clone
+
+    from cobalt_smart_lender_ai_b200.sklearn import XGBClassifier
+    m = XGBClassifier(eval_metric="logloss", use_label_encoder=False, scale_pos_weight=6.7, random_state=42)
+    c = clone(m).set_params(n_estimators=300, max_depth=3, learning_rate=0.05, subsample=0.8, colsample_bytree=0.5, gamma=0)
+    assert c.get_params()["max_depth"] == 3 and c.get_params()["scale_pos_weight"] == 6.7
+    assert m.get_params()["n_estimators"] == 100 and m.get_params()["max_depth"] == 6 and m.get_params()["learning_rate"] == 0.3
+    pickle.loads(pickle.dumps(c))            # an unfitted estimator travels to loky workers
+    from sklearn.exceptions import NotFittedError
+    with pytest.raises(NotFittedError):
+        c.get_booster()
+
+
+def test_quant_shifts_match_oracle_and_bound():
+    from cobalt_smart_lender_ai_b200 import ops
+    from oracle import oracle as O
+    for w in (0.3, 1.0, 1.5, 2.0, 6.746, 8.0, 100.0):
+        sg, sh = ops.quant_shifts(w)
+        assert (sg, sh) == O.quant_shifts(w)
+        assert w * 2.0 ** sg <= 2 ** 17 < w * 2.0 ** (sg + 1) * 1.0000001 * 2 or w * 2.0 ** sg <= 2 ** 17
+
+
+def test_colsample_masks_and_hash_match_oracle_hash():
+    from cobalt_smart_lender_ai_b200.sklearn import _hash32, colsample_masks
+    from oracle import oracle as O
+    for s, a, b in ((78, 0, 0), (78, 3, 1234567), (42, 299, 2 ** 33 + 5)):
+        assert _hash32(s, a, b) == O.lib().orc_hash(s, a, b)
+    m = colsample_masks(5, 20, 0.5, 78)
+    assert m.shape == (5, 20) and (m.sum(1) == 10).all() and len({tuple(r) for r in m}) > 1
+    assert colsample_masks(5, 20, 1.0, 78) is None
+
+
+def test_base_score_estimate():
+    from cobalt_smart_lender_ai_b200.sklearn import estimate_base_score
+    from oracle import oracle as O
+    y = np.array([0] * 870 + [1] * 130)
+    assert estimate_base_score(130 * (870 / 130), 870) == 0.5          # spw = neg/pos -> exactly 0.5 (fixture)
+    assert estimate_base_score(130 * 2.0, 870) == O.estimate_base_score(y, 2.0)
+
+
+def test_shard_rows_and_feature_slices():
+    from cobalt_smart_lender_ai_b200 import parallel
+    for n, w in ((2_200_000, 8), (10, 3), (7, 8)):
+        spans = [parallel.shard_rows(n, r, w) for r in range(w)]
+        assert spans[0][0] == 0 and spans[-1][1] == n
+        assert all(spans[i][1] == spans[i + 1][0] for i in range(w - 1))
+        assert max(e - b for b, e in spans) - min(e - b for b, e in spans) <= 1
+    assert parallel.feature_slices(150, 8)[-1][1] == 150
+
+
+def test_heap_forest_packing_matches_oracle_traversal(fixture_forest):
+    """Complete-tree (heap) repacking of the shipped forest walks to the same leaves as the wire format."""
+    from cobalt_smart_lender_ai_b200.booster import heap_forest, pack_forest
+    from oracle import oracle as O
+    ff = fixture_forest
+    thr, meta, leaf, depth = heap_forest(ff["tree_offsets"], ff["left"], ff["right"], ff["split_index"],
+                                         ff["split_cond"], ff["default_left"])
+    assert depth == 7 and thr.shape == (300, 127) and leaf.shape == (300, 128)
+    rng = np.random.default_rng(0)
+    X = (rng.normal(size=(64, 20)) * 300 + 500).astype(np.float32)
+    X[rng.random(X.shape) < 0.1] = np.nan
+    want = O.predict_margin(X, ff["tree_offsets"], ff["left"], ff["right"], ff["split_index"], ff["split_cond"],
+                            ff["default_left"], 0.0)
+    NI, T = thr.shape[1], thr.shape[0]
+    ar = np.arange(T)
+    for r in range(len(X)):
+        idx = np.zeros(T, np.int64)
+        for _ in range(depth):
+            q = meta[ar, idx].astype(np.int64)
+            v = X[r, q & 0x7FFF]
+            left = np.where(np.isnan(v), (q >> 15) == 1, v < thr[ar, idx])
+            idx = 2 * idx + np.where(left, 1, 2)
+        m = np.float32(0)
+        for x in leaf[ar, idx - NI]:
+            m = np.float32(m + x)
+        assert m.view(np.uint32) == want[r].view(np.uint32)
+    nodes, toff = pack_forest(ff["tree_offsets"], ff["left"], ff["right"], ff["split_index"], ff["split_cond"],
+                              ff["default_left"])
+    assert nodes.shape == (59216,) and toff[-1] == 59216
+
+
+def test_ubjson_roundtrip_and_reference_pickle(fixture_forest):
+    from cobalt_smart_lender_ai_b200 import ubjson
+    ff = fixture_forest
+    names = [str(s) for s in ff["feature_names"]]
+    sub = {k: ff[k][: int(ff["tree_offsets"][5])] for k in ("left", "right", "parent", "split_index", "split_cond",
+                                                           "default_left", "base_weight", "loss_chg", "sum_hess")}
+    sub["tree_offsets"] = ff["tree_offsets"][:6]
+    doc = ubjson.decode(ubjson.encode(ubjson.model_document(sub, names, 0.5)))
+    fo, nm, base = ubjson.forest_from_model(doc)
+    assert nm == names and base == 0.5
+    for k, v in sub.items():
+        assert np.array_equal(fo[k], v), k
+    ref = "/root/reference/src/api/models/xgb_model_tree.pkl"
+    if os.path.exists(ref):                  # only in the build container; the GPU box has the golden npz
+        fo, nm, base = ubjson.forest_from_model(ubjson.decode(ubjson.booster_bytes(ref)))
+        assert nm == names and base == float(ff["base_score"])
+        for k in ("left", "right", "split_index", "default_left", "tree_offsets"):
+            assert np.array_equal(fo[k], ff[k]), k
+        assert np.array_equal(fo["split_cond"].view(np.uint32), ff["split_cond"].view(np.uint32))
+
+
+def test_booster_get_score_semantics(fixture_forest):
+    from cobalt_smart_lender_ai_b200.booster import Booster
+    ff = fixture_forest
+    names = [str(s) for s in ff["feature_names"]]
+    b = Booster(ff, 20, names, 0.5)
+    w = b.get_score(importance_type="weight")
+    assert [int(w[n]) for n in names] == [1926, 690, 3188, 2365, 4789, 657, 1442, 3152, 2299, 423, 1689, 3159, 337, 433,
+                                          320, 522, 520, 205, 428, 914]
+    g, tg = b.get_score(importance_type="gain"), b.get_score(importance_type="total_gain")
+    assert all(abs(g[n] * w[n] - tg[n]) <= 1e-6 * tg[n] for n in names)
+    with pytest.raises(ValueError):
+        b.get_score(importance_type="nope")
+    b2 = pickle.loads(pickle.dumps(b))
+    assert b2.get_score(importance_type="weight") == w
+
+
+def test_api_routes_with_stub_model():
+    """Route logic and JSON shapes of the scoring service mirror (reference src/api/cobalt_fast_api.py:96-143)."""
+    from fastapi.testclient import TestClient
+
+    from cobalt_smart_lender_ai_b200.api import cobalt_fast_api as api
+
+    class _Booster:
+        def get_score(self, importance_type="weight"):
+            return {f"f{i}": float(i) for i in range(15)}
+
+    class _Stub:
+        def predict_proba(self, df):
+            p = np.full(len(df), 0.25, np.float32)
+            return np.stack([1 - p, p], 1)
+
+        def get_booster(self):
+            return _Booster()
+
+    api.xgb_model = _Stub()
+    client = TestClient(api.app)            # no context manager: lifespan (model load) is not run
+    fields = {n: 1.0 for n in ("loan_amnt", "term", "installment", "fico_range_low", "last_fico_range_high",
+                               "open_il_12m", "open_il_24m", "max_bal_bc", "num_rev_accts", "pub_rec_bankruptcies",
+                               "emp_length_num", "earliest_cr_line_days")}
+    fields.update({n: 0 for n in ("grade_E", "home_ownership_MORTGAGE", "verification_status_Verified",
+                                  "application_type_Joint App", "hardship_status_BROKEN", "hardship_status_COMPLETE",
+                                  "hardship_status_COMPLETED", "hardship_status_No Hardship")})
+    r = client.post("/predict", json=fields)
+    assert r.status_code == 200 and r.json()["prob_default"] == 0.25
+    assert r.json()["features"][15] == "application_type_Joint App" and len(r.json()["features"]) == 20
+    csv = "a,b\n1,2\n3,\n"
+    r = client.post("/predict_bulk_csv", files={"file": ("x.csv", csv, "text/csv")})
+    assert r.status_code == 200
+    recs = r.json()["predictions"]
+    assert len(recs) == 2 and recs[0]["prob_default"] == 0.25 and recs[1]["b"] == "null"
+    r = client.post("/feature_importance_bulk", json={"data": [{"x": 1}]})
+    top = r.json()["top_features"]
+    assert len(top) == 10 and top[0] == {"feature": "f14", "importance": 14.0}
+    assert client.post("/feature_importance_bulk", json={"data": []}).status_code == 400
