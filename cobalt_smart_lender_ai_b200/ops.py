@@ -19,6 +19,11 @@ def _ptr(t: torch.Tensor | None) -> C.c_void_p:
     return C.c_void_p(0 if t is None else t.data_ptr())
 
 
+def _ld(X: torch.Tensor) -> int:
+    """Row stride in elements; a single-row tensor may carry any stride for its size-1 dimension."""
+    return int(X.stride(0)) if X.shape[0] > 1 else int(X.shape[1])
+
+
 def _need_cuda(*ts: torch.Tensor) -> None:
     if not torch.cuda.is_available():
         raise _lib.CobaltError("no CUDA device: this package has no CPU path")
@@ -68,7 +73,7 @@ def sketch_cuts(X: torch.Tensor, max_bin: int = 256):
     n_cuts = torch.empty(f, dtype=torch.int32, device=X.device)
     min_vals = torch.empty(f, dtype=torch.float32, device=X.device)
     wp, wb = _aligned(ws)
-    check(lib.cb_sketch_cuts(_ptr(X), n, f, X.stride(0), max_bin, _ptr(cuts), _ptr(n_cuts), _ptr(min_vals), wp, wb,
+    check(lib.cb_sketch_cuts(_ptr(X), n, f, _ld(X), max_bin, _ptr(cuts), _ptr(n_cuts), _ptr(min_vals), wp, wb,
                              _stream()))
     return cuts, n_cuts, min_vals
 
@@ -103,7 +108,7 @@ def bin_pack(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, ldb: int
     ldb = ldb or padded_ldb(f)
     assert pos_feature is None or (pos_feature.dtype == torch.int32 and pos_feature.numel() == ldb)
     bins = torch.empty((n, ldb), dtype=torch.uint8, device=X.device)
-    check(_lib.load().cb_bin_pack_u8(_ptr(X), n, f, X.stride(0), _ptr(cuts), _ptr(n_cuts), _ptr(pos_feature),
+    check(_lib.load().cb_bin_pack_u8(_ptr(X), n, f, _ld(X), _ptr(cuts), _ptr(n_cuts), _ptr(pos_feature),
                                      _ptr(bins), ldb, int(bool(blocked)), _stream()))
     return bins
 
@@ -188,7 +193,7 @@ def predict(X: torch.Tensor, nodes: torch.Tensor, tree_off: torch.Tensor, base_m
     n, f = X.shape
     m = torch.empty(n, dtype=torch.float32, device=X.device) if want_margin else None
     p = torch.empty(n, dtype=torch.float32, device=X.device) if want_proba else None
-    check(_lib.load().cb_predict(_ptr(X), n, f, X.stride(0), _ptr(nodes), _ptr(tree_off), tree_off.numel() - 1,
+    check(_lib.load().cb_predict(_ptr(X), n, f, _ld(X), _ptr(nodes), _ptr(tree_off), tree_off.numel() - 1,
                                  float(base_margin), _ptr(m), _ptr(p), _stream()))
     return m, p
 
@@ -208,6 +213,6 @@ def predict_heap(X: torch.Tensor, nodes: torch.Tensor, leaf: torch.Tensor, depth
     n, f = X.shape
     m = torch.empty(n, dtype=torch.float32, device=X.device) if want_margin else None
     p = torch.empty(n, dtype=torch.float32, device=X.device) if want_proba else None
-    check(_lib.load().cb_predict_heap(_ptr(X), n, f, X.stride(0), _ptr(nodes), _ptr(leaf), int(n_trees), depth,
+    check(_lib.load().cb_predict_heap(_ptr(X), n, f, _ld(X), _ptr(nodes), _ptr(leaf), int(n_trees), depth,
                                       float(base_margin), _ptr(m), _ptr(p), _stream()))
     return m, p
