@@ -93,6 +93,7 @@ _SIGS = {
     "cb_hist_subtract": (C.c_int, [_VP, _VP, _VP, _I64, _VP]),
     "cb_split_scan_workspace_bytes": (C.c_int, [_I, C.POINTER(_SZ)]),
     "cb_split_scan": (C.c_int, [_VP, _VP, _I, _VP, _VP, _VP, C.POINTER(TreeParams), _VP, _VP, _VP, _SZ, _VP]),
+    "cb_split_scan_noalloc": (C.c_int, [_VP, _VP, _I, _VP, _VP, _VP, C.POINTER(TreeParams), _VP, _VP, _VP]),
     "cb_partition_workspace_bytes": (C.c_int, [_I64, C.POINTER(_SZ)]),
     "cb_partition_stable": (C.c_int, [_VP, _I64, _VP, _I64, _I, _I, _I, _VP, _VP, _VP, _SZ, _VP]),
     "cb_predict": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _I, _F, _VP, _VP, _VP]),

@@ -1,5 +1,6 @@
 // libcobalt_gbdt.so -- C ABI over the sm_100a kernels (see include/cobalt_gbdt.h).
 #include <cstdlib>
+#include <mutex>
 #include <new>
 
 #include "sketch.cuh"
@@ -242,6 +243,59 @@ int cb_split_scan(const int64_t* hist, const int32_t* bin_ptr, int f, const floa
   if (ws_bytes < need) return fail(CB_ERR_WORKSPACE, "cb_split_scan: workspace %zu < %zu bytes", ws_bytes, need);
   cudaStream_t s = (cudaStream_t)stream;
   FeatBest* fbuf = Bump(ws).take<FeatBest>((size_t)f);
+  scan_single_kernel<<<ceil_div(f, 4), 128, 0, s>>>(hist, bin_ptr, f, totals, *params, feature_mask, fbuf);
+  pick_single_kernel<<<1, 1, 0, s>>>(fbuf, f, cuts, min_vals, totals, out);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+// ---------------------------------------------------------------------------- K5 without a workspace
+}  // extern "C"
+
+// Scratch of cb_split_scan_noalloc: one candidate record per feature.  It lives in the module's
+// device image (128 KB on every GPU that loads the library, until the process exits).
+#define CB_NOALLOC_MAX_FEATURES 4096
+static __device__ __align__(256) cb::FeatBest g_noalloc_feat_best[CB_NOALLOC_MAX_FEATURES];
+
+namespace cb {
+// Device address of g_noalloc_feat_best on the current device.  In host code the array's name only
+// stands for the symbol, so the address has to be asked for, once per device, with that device current.
+static int noalloc_scratch(FeatBest** out) {
+  constexpr int kMaxDev = 64;
+  static std::mutex mu;
+  static FeatBest* ptrs[kMaxDev] = {nullptr};
+  int dev = 0;
+  CB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDev) return fail(CB_ERR_UNSUPPORTED, "cb_split_scan_noalloc: device index %d not supported", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    FeatBest* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_feat_best);
+    if (e != cudaSuccess || !p)
+      return fail(CB_ERR_CUDA, "cb_split_scan_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return CB_OK;
+}
+}  // namespace cb
+
+extern "C" {
+
+int cb_split_scan_noalloc(const int64_t* hist, const int32_t* bin_ptr, int f, const float* cuts, const float* min_vals,
+                          const int64_t* totals, const cb_tree_params* params, const uint8_t* feature_mask,
+                          cb_split* out, void* stream) {
+  if (!hist || !bin_ptr || !cuts || !min_vals || !totals || !params || !out || f <= 0)
+    return fail(CB_ERR_INVALID, "cb_split_scan_noalloc: bad arguments");
+  if (f > CB_NOALLOC_MAX_FEATURES)
+    return fail(CB_ERR_UNSUPPORTED, "cb_split_scan_noalloc: %d features exceed the built-in scratch of %d; use cb_split_scan with a workspace",
+                f, CB_NOALLOC_MAX_FEATURES);
+  FeatBest* fbuf = nullptr;
+  int rc = noalloc_scratch(&fbuf);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  // every record in [0, f) is written by the first kernel before the second reads it, so nothing
+  // left over from an earlier call (possibly with more features) can be picked up
   scan_single_kernel<<<ceil_div(f, 4), 128, 0, s>>>(hist, bin_ptr, f, totals, *params, feature_mask, fbuf);
   pick_single_kernel<<<1, 1, 0, s>>>(fbuf, f, cuts, min_vals, totals, out);
   CB_LAUNCH_CHECK();

@@ -117,6 +117,23 @@ int cb_split_scan(const int64_t* hist, const int32_t* bin_ptr, int n_features, c
                   void* stream);
 int cb_split_scan_workspace_bytes(int n_features, size_t* bytes);
 
+/* ---- K5 for hosts that hand over inputs and outputs only.
+ * No counterpart in the reference: this entry point exists for callers that are not able to give the
+ * library a workspace -- a serving process whose device memory is carved up once at start-up and
+ * where a later cudaMalloc is forbidden (it stalls every stream of the device and can fail when the
+ * pool is full), or a foreign-language binding that can only pass the buffers it owns.  Same result
+ * as cb_split_scan, bit for bit.  The per-feature candidate records live in an array inside the
+ * library's device image (128 KB per GPU for the life of the process), which bounds the size:
+ * n_features <= 4096, larger inputs are refused with CB_ERR_UNSUPPORTED.  It allocates nothing.
+ *   - The first call on each device looks up the array's device address; make that call before
+ *     any stream capture begins on that device.
+ *   - All calls share the one array.  Each call overwrites the records it reads, so earlier contents
+ *     never leak into a result, but two calls whose kernels overlap on the GPU (different streams,
+ *     or different host threads on one device) race on it: keep them on one stream or serialise them. */
+int cb_split_scan_noalloc(const int64_t* hist, const int32_t* bin_ptr, int n_features, const float* cuts,
+                          const float* min_vals, const int64_t* totals, const cb_tree_params* params,
+                          const uint8_t* feature_mask, cb_split* out, void* stream);
+
 /* ---- K6 stable row partition by compaction (R8).  Replaces RowPartitioner.
  * seg_in/seg_out: u32 [count]; n_left: int64 [1] (device). */
 int cb_partition_workspace_bytes(int64_t count, size_t* bytes);
