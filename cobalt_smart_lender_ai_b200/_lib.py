@@ -47,7 +47,7 @@ class TrainConfig(C.Structure):
 
 class TrainBuffers(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in (
-        "bins", "y", "weight", "margin", "bin_ptr", "cuts", "min_vals", "pos_feature", "left", "right", "parent", "split_index",
+        "bins", "y", "weight", "margin", "bin_ptr", "cuts", "min_vals", "pos_feature", "bins_cm", "left", "right", "parent", "split_index",
         "split_bin", "split_cond", "default_left", "base_weight", "loss_chg", "sum_hess", "n_nodes")]
 
 
@@ -86,6 +86,7 @@ _SIGS = {
     "cb_sketch_cuts": (C.c_int, [_VP, _I64, _I, _I64, _I, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "cb_plan_layout": (C.c_int, [_VP, _I, _I64, _VP, C.POINTER(C.c_int32)]),
     "cb_bin_pack_u8": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _VP, _VP, _I64, _I, _VP]),
+    "cb_bin_transpose_u8": (C.c_int, [_VP, _I64, _I64, _I, _VP, _VP]),
     "cb_grad_logistic_q": (C.c_int, [_VP, _VP, _VP, _I64, _F, _I, _I, _U32, _U32, _U32, _I64, _VP, _VP, _VP]),
     "cb_sigmoid": (C.c_int, [_VP, _I64, _VP, _VP]),
     "cb_hist_workspace_bytes": (C.c_int, [_I64, _I, C.POINTER(_SZ)]),

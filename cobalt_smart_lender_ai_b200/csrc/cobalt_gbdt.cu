@@ -105,6 +105,15 @@ int cb_bin_pack_u8(const float* X, int64_t n, int f, int64_t ldx, const float* c
   return CB_OK;
 }
 
+int cb_bin_transpose_u8(const uint8_t* bins, int64_t n, int64_t ldb, int blocked, uint8_t* bins_cm, void* stream) {
+  if (!bins || !bins_cm || n < 0 || ldb <= 0 || (ldb & 3)) return fail(CB_ERR_INVALID, "cb_bin_transpose_u8: bad arguments");
+  if (n == 0) return CB_OK;
+  bin_transpose_kernel<<<dim3((unsigned)((n + 31) / 32), (unsigned)((ldb + 31) / 32)), 256, 0, (cudaStream_t)stream>>>(
+      make_view(bins, n, ldb, blocked), n, bins_cm);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
 // ---------------------------------------------------------------------------- K3
 int cb_grad_logistic_q(const float* margin, const uint8_t* y, const float* weight, int64_t n, float spw, int sg,
                        int sh, uint32_t keep_thresh, uint32_t seed, uint32_t tree, int64_t row_offset,
@@ -665,7 +674,10 @@ int cb_trainer_level_hist(cb_trainer* t, int level, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   const int nb = level == 0 ? 1 : (1 << (level - 1));
   if (t->cf) {
-    CB_CUDA(cudaMemsetAsync(t->level_buf, 0, sizeof(int64_t) * (size_t)nb * t->S2, s));
+    const int gx = ceil_div(t->cf_R * 32 / 4, 256);
+    int nz = (2 * t->di.sm_count) / (gx * nb);
+    nz = nz < 1 ? 1 : (nz > 16 ? 16 : nz);
+    if (nz > 1) CB_CUDA(cudaMemsetAsync(t->level_buf, 0, sizeof(int64_t) * (size_t)nb * t->S2, s));
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
     const BinsView bv = make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked);
     if (t->identity)
@@ -677,11 +689,8 @@ int cb_trainer_level_hist(cb_trainer* t, int level, void* stream) {
           t->buf.bins, bv.blocked ? t->cfg.n_rows : 0, bv.blocked ? bv.last_w : (int)t->cfg.ldb, t->gpair,
           t->rows[t->cur], t->plan, t->cf_lay, t->cf_fold_src, t->cf_fold_dst, t->partials);
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[1], s));
-    const int tiles = ceil_div(t->cf_R, 32);
-    int nz = (2 * t->di.sm_count) / (tiles * nb);
-    nz = nz < 1 ? 1 : (nz > 16 ? 16 : nz);
-    hist_reduce_cf_kernel<<<dim3(tiles, nb, nz), 256, 0, s>>>(t->partials, t->plan, t->cf_R, t->S, t->cf_slot_of,
-                                                             t->level_buf);
+    hist_reduce_cf_kernel<<<dim3(gx, nb, nz), 256, 0, s>>>(t->partials, t->plan, t->cf_R, t->S, t->cf_slot_of,
+                                                          t->level_buf);
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[2], s));
   } else {
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
@@ -728,7 +737,7 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   const int ident = t->identity ? 1 : 0;
   if (level + 1 < D) {
     uint32_t* rout = t->rows[t->cur ^ 1];
-    part_level_flags_kernel<<<t->n_part_tiles, 256, 0, s>>>(make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked), rin, ident, n, t->segs,
+    part_level_flags_kernel<<<t->n_part_tiles, 256, 0, s>>>(make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked), t->buf.bins_cm, rin, ident, n, t->segs,
                                                             t->flag_bits, t->tile_cnt);
     part_level_scan_kernel<<<1, 1024, 0, s>>>(t->tile_cnt, t->n_part_tiles, n, t->flag_bits, t->segs, t->st, level, D,
                                               t->na, t->plan, t->grid, t->cfg.world_size > 1 ? 1 : 0);
@@ -737,7 +746,7 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
     t->cur ^= 1; t->identity = false;
     t->launches += 3;
   } else {
-    final_apply_kernel<<<ceil_div(n, 256), 256, 0, s>>>(make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked), rin, ident, n, t->segs, t->buf.margin);
+    final_apply_kernel<<<ceil_div(n, 256), 256, 0, s>>>(make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked), t->buf.bins_cm, rin, ident, n, t->segs, t->buf.margin);
     t->launches += 1;
   }
   CB_LAUNCH_CHECK();

@@ -231,48 +231,56 @@ hist_accum_cf_kernel(const uint8_t* __restrict__ bins, int64_t n_rows, int last_
   }
 }
 
-// level buffer [slot][S][2] int64 += sum over a z-slice of the node's partials, un-permuted through
-// slot_of.  The level buffer must be zero before the launch (atomic adds from the z-slices).
+// level buffer [slot][S][2] int64 (+)= sum over a z-slice of the node's int32 partials, un-permuted
+// through slot_of.  Each thread owns 4 consecutive shared-memory-order words of G and of H (16-byte
+// loads, 4 partials in flight).  With gridDim.z > 1 the z-slices add atomically into a zeroed buffer;
+// with gridDim.z == 1 the result is stored directly.
 __global__ void __launch_bounds__(256) hist_reduce_cf_kernel(const int32_t* __restrict__ partials,
                                                              const HistPlan* __restrict__ plan, int R, int S,
                                                              const int32_t* __restrict__ slot_of,
                                                              int64_t* __restrict__ level_buf) {
-  __shared__ long long tg[32][33], th[32][33];
   const int j = blockIdx.y;
   if (j >= plan->n_build) return;
+  const int RW = R * 32;
+  const int v = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (v >= RW) return;
   const int p0 = plan->b_pbeg[j], p1 = plan->b_pbeg[j + 1];
   const int np = p1 - p0, nz = gridDim.z;
   const int per = (np + nz - 1) / nz;
   const int pa = p0 + blockIdx.z * per, pb = min(p1, pa + per);
-  if (pa >= pb) return;
-  const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
-  const int r0 = blockIdx.x * 32;
-  const size_t RW = (size_t)R * 32;
   long long g[4] = {0, 0, 0, 0}, h[4] = {0, 0, 0, 0};
-  for (int p = pa; p < pb; ++p) {
-    const int32_t* pp = partials + (size_t)p * 2 * RW;
+  const int32_t* pp = partials + (size_t)pa * 2 * RW + v;
+  int p = pa;
+  for (; p + 4 <= pb; p += 4, pp += (size_t)8 * RW) {
+    int4 a[4], c[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int r = r0 + wq * 4 + i;
-      if (r < R) {
-        g[i] += __ldg(pp + (size_t)r * 32 + lane);
-        h[i] += __ldg(pp + RW + (size_t)r * 32 + lane);
-      }
+    for (int u = 0; u < 4; ++u) {
+      a[u] = __ldg(reinterpret_cast<const int4*>(pp + (size_t)u * 2 * RW));
+      c[u] = __ldg(reinterpret_cast<const int4*>(pp + (size_t)u * 2 * RW + RW));
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      g[0] += a[u].x; g[1] += a[u].y; g[2] += a[u].z; g[3] += a[u].w;
+      h[0] += c[u].x; h[1] += c[u].y; h[2] += c[u].z; h[3] += c[u].w;
     }
   }
+  for (; p < pb; ++p, pp += (size_t)2 * RW) {
+    const int4 a = __ldg(reinterpret_cast<const int4*>(pp));
+    const int4 c = __ldg(reinterpret_cast<const int4*>(pp + RW));
+    g[0] += a.x; g[1] += a.y; g[2] += a.z; g[3] += a.w;
+    h[0] += c.x; h[1] += c.y; h[2] += c.z; h[3] += c.w;
+  }
+  const int4 so = __ldg(reinterpret_cast<const int4*>(slot_of + v));
+  const int sl[4] = {so.x, so.y, so.z, so.w};
+  long long* out = reinterpret_cast<long long*>(level_buf) + (size_t)j * 2 * S;
 #pragma unroll
-  for (int i = 0; i < 4; ++i) { tg[wq * 4 + i][lane] = g[i]; th[wq * 4 + i][lane] = h[i]; }
-  __syncthreads();
-  unsigned long long* out = reinterpret_cast<unsigned long long*>(level_buf) + (size_t)j * 2 * S;
-  for (int it = 0; it < 4; ++it) {
-    const int bank = wq * 4 + it, rr = lane, r = r0 + rr;      // consecutive lanes -> consecutive bins of one bank
-    if (r < R) {
-      const int s = __ldg(slot_of + (size_t)r * 32 + bank);
-      if (s >= 0) {
-        const long long a = tg[rr][bank], b = th[rr][bank];
-        if (a) atomicAdd(out + 2 * (size_t)s, (unsigned long long)a);
-        if (b) atomicAdd(out + 2 * (size_t)s + 1, (unsigned long long)b);
-      }
+  for (int i = 0; i < 4; ++i) {
+    if (sl[i] < 0) continue;
+    if (nz == 1) {
+      reinterpret_cast<longlong2*>(out)[sl[i]] = make_longlong2(g[i], h[i]);
+    } else {
+      if (g[i]) atomicAdd(reinterpret_cast<unsigned long long*>(out) + 2 * (size_t)sl[i], (unsigned long long)g[i]);
+      if (h[i]) atomicAdd(reinterpret_cast<unsigned long long*>(out) + 2 * (size_t)sl[i] + 1, (unsigned long long)h[i]);
     }
   }
 }

@@ -23,11 +23,12 @@ __device__ __forceinline__ uint32_t bin_of(float x, const float* __restrict__ c,
 struct BinsView {
   const uint8_t* base;
   int64_t n_rows, ldb;
+  int64_t n_rows_cm;       // row count of the position-major copy (always the true row count)
   int blocked, n_blocks, last_w;
 };
 __host__ __device__ inline BinsView make_view(const uint8_t* base, int64_t n_rows, int64_t ldb, int blocked) {
   BinsView v;
-  v.base = base; v.n_rows = n_rows; v.ldb = ldb; v.blocked = blocked;
+  v.base = base; v.n_rows = n_rows; v.ldb = ldb; v.blocked = blocked; v.n_rows_cm = n_rows;
   v.n_blocks = (int)((ldb + 127) / 128);
   v.last_w = (int)(ldb - 128 * (int64_t)(v.n_blocks - 1));
   if (v.n_blocks <= 1) v.blocked = 0;
@@ -59,6 +60,25 @@ __global__ void __launch_bounds__(256) bin_pack_kernel(const float* __restrict__
     out |= code << (8 * j);
   }
   *reinterpret_cast<uint32_t*>(bins + byte_index(view, row, 4 * w)) = out;
+}
+
+// position-major copy of the binned matrix: out[p][row] = code of column position p (32 x 32 byte tiles)
+__global__ void __launch_bounds__(256) bin_transpose_kernel(BinsView view, int64_t n, uint8_t* __restrict__ out) {
+  __shared__ uint8_t t[32][33];
+  const int64_t r0 = (int64_t)blockIdx.x * 32;
+  const int p0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int k = ty; k < 32; k += 8) {
+    const int64_t r = r0 + k;
+    const int p = p0 + tx;
+    t[k][tx] = (r < n && p < view.ldb) ? view.base[byte_index(view, r, p)] : (uint8_t)CB_MISSING_BIN;
+  }
+  __syncthreads();
+  for (int k = ty; k < 32; k += 8) {
+    const int p = p0 + k;
+    const int64_t r = r0 + tx;
+    if (p < view.ldb && r < n) out[(size_t)p * n + r] = t[tx][k];
+  }
 }
 
 // =====================================================================================

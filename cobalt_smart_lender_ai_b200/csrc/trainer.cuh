@@ -203,29 +203,61 @@ struct SegCache {
   int begin[kMaxLevelNodes], count[kMaxLevelNodes];
 };
 
+// packed per-segment split description cached in shared memory: feat | dl << 16 | kind << 24, split bin
+struct SegSplit { int meta[kMaxLevelNodes]; int bin[kMaxLevelNodes]; };
+
+// the code of column position `pos` of `row`: from the position-major copy when there is one
+// (consecutive rows of a node are close together there: a level's gathers touch ~2^level bytes per
+// row instead of a DRAM burst per row), else from the row/block-major matrix
+__device__ __forceinline__ int code_at(const BinsView& v, const uint8_t* __restrict__ bins_cm, uint32_t row, int pos) {
+  if (bins_cm) return __ldg(bins_cm + (size_t)pos * v.n_rows_cm + row);
+  return __ldg(v.base + byte_index(v, row, pos));
+}
+
 // P1: go-left flags of every position that sits in a node being split (kind 1)
-__global__ void __launch_bounds__(256) part_level_flags_kernel(BinsView view,
+__global__ void __launch_bounds__(256) part_level_flags_kernel(BinsView view, const uint8_t* __restrict__ bins_cm,
                                                                const uint32_t* __restrict__ rows_in, int identity,
                                                                int n_rows, const LevelSegs* __restrict__ segs,
                                                                uint32_t* __restrict__ flag_bits,
                                                                int* __restrict__ tile_cnt) {
   __shared__ SegCache sc;
+  __shared__ SegSplit ss;
   __shared__ int wsum[8];
   const int n = segs->n;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) { sc.begin[i] = segs->begin[i]; sc.count[i] = segs->count[i]; }
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    sc.begin[i] = segs->begin[i]; sc.count[i] = segs->count[i];
+    ss.meta[i] = segs->feat[i] | (segs->dl[i] << 16) | (segs->kind[i] << 24);
+    ss.bin[i] = segs->bin[i];
+  }
   __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int tile0 = blockIdx.x * kPartTile;
+  constexpr int IT = kPartTile / 256;
+  uint32_t row[IT];
+  int seg[IT];
+#pragma unroll
+  for (int it = 0; it < IT; ++it) {            // all row indices first: 8 independent loads in flight
+    const int pos = tile0 + wid * (kPartTile / 8) + it * 32 + lane;
+    row[it] = 0; seg[it] = -1;
+    if (pos < n_rows) {
+      row[it] = identity ? (uint32_t)pos : __ldg(rows_in + pos);
+      seg[it] = find_seg(sc.begin, sc.count, n, pos);
+    }
+  }
+  int code[IT];
+#pragma unroll
+  for (int it = 0; it < IT; ++it) {            // then all gathers
+    code[it] = -1;
+    if (seg[it] >= 0 && (ss.meta[seg[it]] >> 24) == 1) code[it] = code_at(view, bins_cm, row[it], ss.meta[seg[it]] & 0xFFFF);
+  }
   int cnt = 0;
-  for (int it = 0; it < kPartTile / 256; ++it) {
+#pragma unroll
+  for (int it = 0; it < IT; ++it) {
     const int pos = tile0 + wid * (kPartTile / 8) + it * 32 + lane;
     bool fl = false;
-    if (pos < n_rows) {
-      const int i = find_seg(sc.begin, sc.count, n, pos);
-      if (i >= 0 && segs->kind[i] == 1) {
-        const uint32_t row = identity ? (uint32_t)pos : __ldg(rows_in + pos);
-        fl = goes_left(view, row, segs->feat[i], segs->bin[i], segs->dl[i]);
-      }
+    if (code[it] >= 0) {
+      const int m = ss.meta[seg[it]];
+      fl = code[it] == CB_MISSING_BIN ? ((m >> 16) & 1) != 0 : code[it] <= ss.bin[seg[it]];
     }
     const uint32_t bal = __ballot_sync(0xffffffffu, fl);
     if (lane == 0 && pos < n_rows) flag_bits[pos >> 5] = bal;
@@ -358,7 +390,7 @@ __global__ void __launch_bounds__(256) part_level_scatter_kernel(const uint32_t*
 }
 
 // last level: children are leaves, so rows are not moved; each row takes its child's leaf value
-__global__ void __launch_bounds__(256) final_apply_kernel(BinsView view,
+__global__ void __launch_bounds__(256) final_apply_kernel(BinsView view, const uint8_t* __restrict__ bins_cm,
                                                           const uint32_t* __restrict__ rows_in, int identity,
                                                           int n_rows, const LevelSegs* __restrict__ segs,
                                                           float* __restrict__ margin) {
@@ -372,7 +404,11 @@ __global__ void __launch_bounds__(256) final_apply_kernel(BinsView view,
   if (i < 0) return;
   const uint32_t row = identity ? (uint32_t)pos : __ldg(rows_in + pos);
   float leaf = segs->leafL[i];
-  if (segs->kind[i] == 2 && !goes_left(view, row, segs->feat[i], segs->bin[i], segs->dl[i])) leaf = segs->leafR[i];
+  if (segs->kind[i] == 2) {
+    const int c = code_at(view, bins_cm, row, segs->feat[i]);
+    const bool left = c == CB_MISSING_BIN ? segs->dl[i] != 0 : c <= segs->bin[i];
+    if (!left) leaf = segs->leafR[i];
+  }
   margin[row] = __fadd_rn(margin[row], leaf);
 }
 

@@ -173,6 +173,7 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
             pos = torch.from_numpy(pos_np).to(dev)
             bins = ops.bin_pack(Xd, cuts, n_cuts, pos_feature=pos, blocked=_cf)
             del Xd
+            bins_cm = ops.bin_transpose(bins, blocked=_cf)
             bin_ptr = ops.bin_ptr_of(n_cuts)
             T = int(self.n_estimators)
             seed = int(self.random_state or 0)
@@ -183,7 +184,7 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
                             reg_alpha=float(self.reg_alpha), gamma=float(self.gamma),
                             min_child_weight=float(self.min_child_weight), scale_pos_weight=spw, sg=sg, sh=sh,
                             subsample=float(self.subsample), seed=seed, max_trees=max(T, 1),
-                            base_margin=base_margin_of(base_score), row_offset=row_offset, pos_feature=pos, blocked=_cf)
+                            base_margin=base_margin_of(base_score), row_offset=row_offset, pos_feature=pos, blocked=_cf, bins_cm=bins_cm)
             tr.boost(T, masks_d)
             forest = tr.forest_numpy()
             self._gpu_launches = tr.launch_count()

@@ -29,7 +29,8 @@ class GpuTrainer:
                  eta: float = 0.3, reg_lambda: float = 1.0, reg_alpha: float = 0.0, gamma: float = 0.0,
                  min_child_weight: float = 1.0, scale_pos_weight: float = 1.0, sg: int, sh: int,
                  subsample: float = 1.0, seed: int = 0, max_trees: int = 100, base_margin: float = 0.0,
-                 row_offset: int = 0, group=None, pos_feature: torch.Tensor | None = None, blocked: bool = False):
+                 row_offset: int = 0, group=None, pos_feature: torch.Tensor | None = None, blocked: bool = False,
+                 bins_cm: torch.Tensor | None = None):
         if not bins.is_cuda:
             raise _lib.CobaltError("GpuTrainer needs CUDA tensors: this package has no CPU path")
         self.lib = _lib.load()
@@ -46,6 +47,7 @@ class GpuTrainer:
         self.bins, self.y, self.weight = bins, y.to(torch.uint8).contiguous(), weight
         self.bin_ptr, self.cuts, self.min_vals = bin_ptr, cuts, min_vals
         self.pos_feature = pos_feature
+        self.bins_cm = bins_cm
         self.margin = torch.full((n,), float(base_margin), dtype=torch.float32, device=self.dev)
         self.forest = {k: torch.zeros((max_trees, self.max_nodes), dtype=dt, device=self.dev) for k, dt in FOREST_FIELDS}
         self.n_nodes = torch.zeros(max_trees, dtype=torch.int32, device=self.dev)
@@ -61,7 +63,7 @@ class GpuTrainer:
         self._ws_base = wp.value
         p = lambda t: None if t is None else t.data_ptr()  # noqa: E731
         self.buffers = TrainBuffers(p(self.bins), p(self.y), p(self.weight), p(self.margin), p(self.bin_ptr),
-                                    p(self.cuts), p(self.min_vals), p(self.pos_feature), *[p(self.forest[k]) for k, _ in FOREST_FIELDS],
+                                    p(self.cuts), p(self.min_vals), p(self.pos_feature), p(self.bins_cm), *[p(self.forest[k]) for k, _ in FOREST_FIELDS],
                                     p(self.n_nodes))
         h = C.c_void_p()
         check(self.lib.cb_trainer_create(C.byref(self.cfg), C.byref(self.buffers), wp, wb, C.byref(h)))

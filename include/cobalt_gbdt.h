@@ -72,6 +72,11 @@ int cb_bin_pack_u8(const float* X, int64_t n_rows, int n_features, int64_t ldx, 
                    const int32_t* n_cuts, const int32_t* pos_feature, uint8_t* bins, int64_t ldb, int blocked,
                    void* stream);
 
+/* position-major copy of a binned matrix: bins_cm[p * n + row] = byte p of `row`.  Optional input of the
+ * trainer: the row partition (K6) reads one byte per row of the split feature, and rows of a node are
+ * ascending, so this copy turns a DRAM burst per row into a near-sequential read.  No reference counterpart. */
+int cb_bin_transpose_u8(const uint8_t* bins, int64_t n_rows, int64_t ldb, int blocked, uint8_t* bins_cm, void* stream);
+
 /* ---- K3 logistic gradient/hessian in fixed point (R4).
  * Replaces the binary:logistic objective with scale_pos_weight
  * (src/model_train_test/model_tree_train_test.py:103-116).
@@ -188,6 +193,7 @@ typedef struct {
   const float* cuts;       /* [f][256] */
   const float* min_vals;   /* [f] */
   const int32_t* pos_feature; /* [ldb] column placement used when the rows were binned, or NULL */
+  const uint8_t* bins_cm;  /* [ldb][n] position-major copy (cb_bin_transpose_u8), or NULL */
   /* forest out, each [max_trees][max_nodes], max_nodes = 2^(max_depth+1)-1 (wire format a-9) */
   int32_t* left; int32_t* right; int32_t* parent; int32_t* split_index; int32_t* split_bin;
   float* split_cond; uint8_t* default_left; float* base_weight; float* loss_chg; float* sum_hess;

@@ -231,7 +231,8 @@ def _block_major(b):
     return np.concatenate(parts).reshape(n, ldb)
 
 
-def _train_gpu(ops, ref, X, y, n_trees, spw, subsample=1.0, seed=0, masks=None, weight=None, natural=False, **kw):
+def _train_gpu(ops, ref, X, y, n_trees, spw, subsample=1.0, seed=0, masks=None, weight=None, natural=False,
+               with_cm=True, **kw):
     from cobalt_smart_lender_ai_b200.trainer import GpuTrainer
     tp = ref["tp"]
     pos, _cf = None, False
@@ -248,7 +249,8 @@ def _train_gpu(ops, ref, X, y, n_trees, spw, subsample=1.0, seed=0, masks=None, 
                     reg_lambda=tp.reg_lambda, reg_alpha=tp.reg_alpha, gamma=tp.gamma,
                     min_child_weight=tp.min_child_weight, scale_pos_weight=spw, sg=tp.sg, sh=tp.sh,
                     subsample=subsample, seed=seed, max_trees=n_trees, base_margin=O.base_margin_of(ref["base_score"]),
-                    group=False, pos_feature=pos, blocked=_cf)
+                    group=False, pos_feature=pos, blocked=_cf,
+                    bins_cm=ops.bin_transpose(bins, blocked=_cf) if with_cm else None)
     tr.boost(n_trees, None if masks is None else _dev(masks))
     return tr
 
@@ -357,6 +359,9 @@ def test_train_150_features_two_column_blocks(ops):
     _assert_forest_equal(tr.forest_numpy(), ref["flat"])
     assert np.array_equal(tr.margin.cpu().numpy().view(np.uint32), ref["margin"].view(np.uint32))
     assert np.array_equal(tr.node_hist(0).cpu().numpy(), ref["forest"]["root_hist"])
+    tr2 = _train_gpu(ops, ref, X, y, 4, spw, with_cm=False)        # without the position-major copy
+    _assert_forest_equal(tr2.forest_numpy(), ref["flat"])
+    assert torch.equal(tr2.margin, tr.margin)
     assert np.array_equal(_final_rows(ref, tr, ref["bins"]), ref["forest"]["row_order"])
 
 
