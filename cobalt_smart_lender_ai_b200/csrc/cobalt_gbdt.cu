@@ -726,13 +726,12 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   const int nb = level == 0 ? 1 : (1 << (level - 1));
   const int ln = 1 << level;
   const int n = (int)t->cfg.n_rows;
-  hist_finalize_kernel<<<dim3(ceil_div(t->S2, 256), nb), 256, 0, s>>>(t->level_buf, t->plan, t->S2, t->pool, t->na,
-                                                                      level == 0 ? t->level_buf + t->S2 : nullptr);
-  scan_level_kernel<<<dim3(ceil_div(t->cfg.n_features, 4), ln), 128, 0, s>>>(
-      t->pool, t->buf.bin_ptr, t->cfg.n_features, t->S2, t->st, level, t->na, t->cfg.tree, t->fmask, t->feat_best);
+  scan_level_fused_kernel<<<dim3(t->cfg.n_features, ln), 128, 0, s>>>(
+      t->level_buf, t->pool, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S, t->st, level, t->na, t->cfg.tree, t->fmask,
+      t->feat_best, level == 0 ? t->level_buf + t->S2 : nullptr);
   level_finish_kernel<<<1, 256, 0, s>>>(t->st, level, D, t->feat_best, t->cfg.n_features, t->buf.cuts,
                                         t->buf.min_vals, t->cfg.tree, t->na, tree_out(t), t->segs, t->feat_pos);
-  t->launches += 3;
+  t->launches += 2;
   const uint32_t* rin = t->rows[t->cur];
   const int ident = t->identity ? 1 : 0;
   if (level + 1 < D) {

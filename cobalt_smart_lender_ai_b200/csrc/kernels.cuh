@@ -143,6 +143,7 @@ struct HistPlan {               // lives in device memory
   int b_sibling[kMaxBuild];     // node id derived by subtraction (-1: none)
   int b_parent[kMaxBuild];
   int b_pbeg[kMaxBuild + 1];    // partial range of build slot j: [b_pbeg[j], b_pbeg[j+1])
+  int lvl_src[2 * kMaxBuild];   // level node i -> build slot * 2 + (0 built | 1 sibling = parent - built)
   int cta_slot[kMaxGrid];       // build slot of CTA b (-1: idle)
   int cta_begin[kMaxGrid];      // first position (in row order) of the CTA's slice
   int cta_rows[kMaxGrid];

@@ -48,7 +48,7 @@ __global__ void round_init_kernel(TreeState* st, NodeArrays na, TreeOut to, int 
     st->lvl_first[0] = 0; st->lvl_count[0] = 1;
     na.begin[0] = 0; na.count[0] = n_rows;
     int b0 = 0, c0 = n_rows;
-    plan->b_node[0] = 0; plan->b_sibling[0] = -1; plan->b_parent[0] = -1;
+    plan->b_node[0] = 0; plan->b_sibling[0] = -1; plan->b_parent[0] = -1; plan->lvl_src[0] = 0;
     plan_ctas(plan, 1, &b0, &c0, grid);
   }
 }
@@ -94,6 +94,139 @@ __global__ void __launch_bounds__(128) scan_level_kernel(const int64_t* __restri
   if ((threadIdx.x & 31) == 0) feat_best[(size_t)i * f + feat] = fb;
 }
 
+// K9 + K5 fused, one CTA of 128 threads per (level node, feature), 2 bins per thread:
+// reads the node's histogram from the level buffer (built child) or as parent - built (sibling),
+// stores it in the pool for the next level, and scans it (exact int64 prefix sums, f64 gains).
+__device__ __forceinline__ unsigned long long cand_key(float chg, int tiebreak) {
+  return chg > 0.0f ? ((unsigned long long)__float_as_uint(chg) << 32) | (unsigned)tiebreak : 0ull;
+}
+__global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __restrict__ level_buf,
+                                                               int64_t* __restrict__ pool,
+                                                               const HistPlan* __restrict__ plan,
+                                                               const int32_t* __restrict__ bin_ptr, int f, int S,
+                                                               const TreeState* __restrict__ st, int level,
+                                                               NodeArrays na, cb_tree_params p,
+                                                               const uint8_t* __restrict__ feature_mask,
+                                                               FeatBest* __restrict__ feat_best,
+                                                               const int64_t* __restrict__ tail) {
+  __shared__ long long sg[4], sh[4];
+  __shared__ unsigned long long skf[4], skb[4];
+  const int i = blockIdx.y;
+  if (i >= st->lvl_count[level]) return;
+  const int feat = blockIdx.x;
+  const int nid = st->lvl_first[level] + i;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  long long Gt, Ht;
+  if (level == 0) {
+    Gt = tail[0]; Ht = tail[1];
+    if (feat == 0 && tid == 0) { na.G[0] = Gt; na.H[0] = Ht; }
+  } else {
+    Gt = na.G[nid]; Ht = na.H[nid];
+  }
+  if (feature_mask && !feature_mask[feat]) {
+    if (tid == 0) {
+      FeatBest fb; fb.chg = 0.0f; fb.split_bin = -1; fb.default_left = 0; fb.pad = 0; fb.GL = 0; fb.HL = 0;
+      feat_best[(size_t)i * f + feat] = fb;
+    }
+    return;
+  }
+  const int b0 = __ldg(bin_ptr + feat), nb = __ldg(bin_ptr + feat + 1) - b0;
+  const int src = plan->lvl_src[i], j = src >> 1;
+  const longlong2* lb = reinterpret_cast<const longlong2*>(level_buf) + (size_t)j * S + b0;
+  longlong2* mine = reinterpret_cast<longlong2*>(pool) + (size_t)nid * S + b0;
+  const longlong2* par = (src & 1) ? reinterpret_cast<const longlong2*>(pool) + (size_t)plan->b_parent[j] * S + b0 : nullptr;
+  longlong2 v[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int b = 2 * tid + k;
+    v[k] = make_longlong2(0, 0);
+    if (b < nb) {
+      v[k] = lb[b];
+      if (par) { const longlong2 q = par[b]; v[k].x = q.x - v[k].x; v[k].y = q.y - v[k].y; }
+      mine[b] = v[k];
+    }
+  }
+  // block-wide inclusive scan of the per-thread sums
+  long long tg = v[0].x + v[1].x, th = v[0].y + v[1].y;
+  long long ig = tg, ih = th;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const long long a = __shfl_up_sync(0xffffffffu, ig, o), b = __shfl_up_sync(0xffffffffu, ih, o);
+    if (lane >= o) { ig += a; ih += b; }
+  }
+  if (lane == 31) { sg[wid] = ig; sh[wid] = ih; }
+  __syncthreads();
+  long long wg = 0, wh = 0, Gf = 0, Hf = 0;
+#pragma unroll
+  for (int w = 0; w < 4; ++w) {
+    if (w < wid) { wg += sg[w]; wh += sh[w]; }
+    Gf += sg[w]; Hf += sh[w];
+  }
+  const long long exg = wg + ig - tg, exh = wh + ih - th;     // sum of all bins before 2 * tid
+  const double dg = ldexp(1.0, -p.sg), dh = ldexp(1.0, -p.sh);
+  const float root_gain = __double2float_rn(calc_gain(__dmul_rn((double)Gt, dg), __dmul_rn((double)Ht, dh), p));
+  // forward (missing -> right): candidate b has left = prefix_incl(b); scan order ascending
+  float fc = 0.0f; int fbin = -1;
+  long long pg = exg, ph = exh;
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int b = 2 * tid + k;
+    pg += v[k].x; ph += v[k].y;
+    if (b < nb) {
+      const float c = split_chg(pg, ph, Gt - pg, Ht - ph, dg, dh, root_gain, p);
+      if (c > fc) { fc = c; fbin = b; }
+    }
+  }
+  // backward (missing -> left): candidate b has right = sum of bins >= b; scan order descending
+  float bc = 0.0f; int bbin = -1;
+  const bool has_missing = (Gf != Gt) || (Hf != Ht);
+  if (has_missing) {
+#pragma unroll
+    for (int k = 1; k >= 0; --k) {
+      const int b = 2 * tid + k;
+      if (b < nb) {
+        const long long eg = exg + (k ? v[0].x : 0), eh = exh + (k ? v[0].y : 0);   // prefix_excl(b)
+        const long long gr = Gf - eg, hr = Hf - eh;
+        const float c = split_chg(Gt - gr, Ht - hr, gr, hr, dg, dh, root_gain, p);
+        if (c > bc) { bc = c; bbin = b; }
+      }
+    }
+  }
+  // block arg-max: forward ties -> lower bin, backward ties -> higher bin (first in scan order)
+  unsigned long long kf = cand_key(fc, 0xFFFF - fbin), kb = cand_key(bc, bbin);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long a = __shfl_xor_sync(0xffffffffu, kf, o), b = __shfl_xor_sync(0xffffffffu, kb, o);
+    kf = a > kf ? a : kf; kb = b > kb ? b : kb;
+  }
+  if (lane == 0) { skf[wid] = kf; skb[wid] = kb; }
+  __syncthreads();
+  kf = max(max(skf[0], skf[1]), max(skf[2], skf[3]));
+  kb = max(max(skb[0], skb[1]), max(skb[2], skb[3]));
+  const bool use_b = (unsigned)(kb >> 32) > (unsigned)(kf >> 32);       // backward only when strictly better
+  const unsigned long long kw = use_b ? kb : kf;
+  if (kw == 0ull) {
+    if (tid == 0) {
+      FeatBest fb; fb.chg = 0.0f; fb.split_bin = -1; fb.default_left = 0; fb.pad = 0; fb.GL = 0; fb.HL = 0;
+      feat_best[(size_t)i * f + feat] = fb;
+    }
+    return;
+  }
+  const int cbin = use_b ? (int)(kw & 0xFFFFu) : 0xFFFF - (int)(kw & 0xFFFFu);   // candidate bin
+  const int sbin = use_b ? cbin - 1 : cbin;                                       // rows with code <= sbin go left
+  // the thread that owns bin sbin (or thread 0 when sbin == -1) knows prefix_incl(sbin)
+  const int owner = sbin >= 0 ? sbin >> 1 : 0;
+  if (tid == owner) {
+    long long gl = 0, hl = 0;
+    if (sbin >= 0) { gl = exg + v[0].x + ((sbin & 1) ? v[1].x : 0); hl = exh + v[0].y + ((sbin & 1) ? v[1].y : 0); }
+    if (use_b) { gl += Gt - Gf; hl += Ht - Hf; }
+    FeatBest fb;
+    fb.chg = __uint_as_float((unsigned)(kw >> 32)); fb.split_bin = sbin; fb.default_left = use_b ? 1 : 0; fb.pad = 0;
+    fb.GL = gl; fb.HL = hl;
+    feat_best[(size_t)i * f + feat] = fb;
+  }
+}
+
 // one block: pick each node's best feature, allocate children in node-id order (R9),
 // write the tree arrays, the children's totals and the level's segment table
 __global__ void __launch_bounds__(256) level_finish_kernel(TreeState* st, int level, int max_depth,
@@ -120,7 +253,15 @@ __global__ void __launch_bounds__(256) level_finish_kernel(TreeState* st, int le
       int of = __shfl_xor_sync(0xffffffffu, bf, o);
       if (oc > bc || (oc == bc && of >= 0 && (bf < 0 || of < bf))) { bc = oc; bf = of; }
     }
-    if (lane == 0) { s_chg[i] = bc; s_feat[i] = bf; }
+    if (lane == 0) {
+      s_chg[i] = bc; s_feat[i] = bf;
+      bool valid = false;
+      if (bf >= 0) {
+        const long long HL = feat_best[(size_t)i * f + bf].HL, HR = na.H[first + i] - HL;
+        valid = bc > 1e-6f && !(bc < p.gamma) && level < max_depth && HL != 0 && HR != 0;
+      }
+      s_child[i] = valid ? 1 : 0;
+    }
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -131,14 +272,7 @@ __global__ void __launch_bounds__(256) level_finish_kernel(TreeState* st, int le
     int next = st->n_nodes;
     const int old = next;
     for (int i = 0; i < cnt; ++i) {
-      const int nid = first + i, bf = s_feat[i];
-      bool valid = false;
-      if (bf >= 0) {
-        const FeatBest fb = feat_best[(size_t)i * f + bf];
-        const long long HL = fb.HL, HR = na.H[nid] - fb.HL;
-        valid = s_chg[i] > 1e-6f && !(s_chg[i] < p.gamma) && level < max_depth && HL != 0 && HR != 0;
-      }
-      if (valid) { s_child[i] = next; next += 2; } else s_child[i] = -1;
+      if (s_child[i]) { s_child[i] = next; next += 2; } else s_child[i] = -1;
     }
     st->n_nodes = next;
     st->lvl_first[level + 1] = old;
@@ -327,19 +461,36 @@ __global__ void __launch_bounds__(1024) part_level_scan_kernel(int* __restrict__
     na.begin[L + 1] = bg + nl; na.count[L + 1] = ct - nl;
   }
   __syncthreads();
+  // next level's histogram plan: per split node pick the child to build (parallel), then one thread
+  // numbers the build slots and hands out CTAs (reads shared memory only)
+  __shared__ int b_pick[kMaxLevelNodes];
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    int pick = -1;
+    if (level + 1 < max_depth && segs->kind[i] == 1) {
+      const int L = segs->child[i], R = L + 1;
+      const bool left_small = by_hessian ? (na.H[L] <= na.H[R]) : (na.count[L] <= na.count[R]);
+      pick = left_small ? 0 : 1;
+      part[i] = na.begin[left_small ? L : R];          // reuse the scan scratch: begin of the built child
+      part[kMaxLevelNodes + i] = na.count[left_small ? L : R];
+      b_pick[i] = (L << 1) | pick;
+    }
+    if (pick < 0) b_pick[i] = -1;
+  }
+  __syncthreads();
   if (threadIdx.x == 0) {
     int nb = 0;
-    if (level + 1 < max_depth) {
-      const int first = st->lvl_first[level];
-      for (int i = 0; i < n; ++i) {
-        if (segs->kind[i] != 1) continue;
-        const int L = segs->child[i], R = L + 1;
-        const bool left_small = by_hessian ? (na.H[L] <= na.H[R]) : (na.count[L] <= na.count[R]);
-        const int bn = left_small ? L : R;
-        plan->b_node[nb] = bn; plan->b_sibling[nb] = left_small ? R : L; plan->b_parent[nb] = first + i;
-        b_begin[nb] = na.begin[bn]; b_count[nb] = na.count[bn];
-        ++nb;
-      }
+    const int first = st->lvl_first[level], first_next = st->lvl_first[level + 1];
+    for (int i = 0; i < n; ++i) {
+      if (b_pick[i] < 0) continue;
+      const int L = b_pick[i] >> 1, R = L + 1;
+      const bool left_small = (b_pick[i] & 1) == 0;
+      const int bn = left_small ? L : R;
+      plan->b_node[nb] = bn; plan->b_sibling[nb] = left_small ? R : L; plan->b_parent[nb] = first + i;
+      plan->lvl_src[L - first_next] = 2 * nb + (left_small ? 0 : 1);
+      plan->lvl_src[R - first_next] = 2 * nb + (left_small ? 1 : 0);
+      b_begin[nb] = part[i];
+      b_count[nb] = part[kMaxLevelNodes + i];
+      ++nb;
     }
     plan_ctas(plan, nb, b_begin, b_count, grid);
   }
