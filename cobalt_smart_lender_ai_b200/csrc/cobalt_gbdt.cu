@@ -726,24 +726,24 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   const int nb = level == 0 ? 1 : (1 << (level - 1));
   const int ln = 1 << level;
   const int n = (int)t->cfg.n_rows;
+  FinishArgs fa;
+  fa.max_depth = D; fa.cuts = t->buf.cuts; fa.min_vals = t->buf.min_vals; fa.to = tree_out(t); fa.segs = t->segs;
+  fa.feat_pos = t->feat_pos;
   scan_level_fused_kernel<<<dim3(t->cfg.n_features, ln), 128, 0, s>>>(
       t->level_buf, t->pool, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S, t->st, level, t->na, t->cfg.tree, t->fmask,
-      t->feat_best, level == 0 ? t->level_buf + t->S2 : nullptr);
-  level_finish_kernel<<<1, 256, 0, s>>>(t->st, level, D, t->feat_best, t->cfg.n_features, t->buf.cuts,
-                                        t->buf.min_vals, t->cfg.tree, t->na, tree_out(t), t->segs, t->feat_pos);
-  t->launches += 2;
+      t->feat_best, level == 0 ? t->level_buf + t->S2 : nullptr, t->st, fa);
+  t->launches += 1;
   const uint32_t* rin = t->rows[t->cur];
   const int ident = t->identity ? 1 : 0;
   if (level + 1 < D) {
     uint32_t* rout = t->rows[t->cur ^ 1];
-    part_level_flags_kernel<<<t->n_part_tiles, 256, 0, s>>>(make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked), t->buf.bins_cm, rin, ident, n, t->segs,
-                                                            t->flag_bits, t->tile_cnt);
-    part_level_scan_kernel<<<1, 1024, 0, s>>>(t->tile_cnt, t->n_part_tiles, n, t->flag_bits, t->segs, t->st, level, D,
-                                              t->na, t->plan, t->grid, t->cfg.world_size > 1 ? 1 : 0);
+    part_level_flags_kernel<<<t->n_part_tiles, 256, 0, s>>>(
+        make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked), t->buf.bins_cm, rin, ident, n, t->segs,
+        t->flag_bits, t->tile_cnt, t->segs, t->st, level, D, t->na, t->plan, t->grid, t->cfg.world_size > 1 ? 1 : 0);
     part_level_scatter_kernel<<<t->n_part_tiles, 256, 0, s>>>(rin, ident, n, t->segs, t->flag_bits, t->tile_cnt, rout,
                                                               t->buf.margin);
     t->cur ^= 1; t->identity = false;
-    t->launches += 3;
+    t->launches += 2;
   } else {
     final_apply_kernel<<<ceil_div(n, 256), 256, 0, s>>>(make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked), t->buf.bins_cm, rin, ident, n, t->segs, t->buf.margin);
     t->launches += 1;

@@ -13,6 +13,8 @@ struct TreeState {                        // device memory
   int lvl_count[kMaxDepth + 2];
   int pad_;
   long long root_tot[2];                  // local sum of (q_g, q_h), filled by the gradient kernel
+  unsigned int done[2 * (kMaxDepth + 2)]; // per level: CTAs finished in the scan / flags kernels (last one runs the epilogue)
+  unsigned long long best_key[kMaxLevelNodes];  // per level node: max over features of (chg bits << 32 | 0xFFFF - feature)
 };
 
 // the level's nodes in id order (= ascending position order): what the partition pass needs
@@ -44,8 +46,9 @@ __global__ void round_init_kernel(TreeState* st, NodeArrays na, TreeOut to, int 
   }
   if (i == 0) {
     st->n_nodes = 1;
-    for (int l = 0; l < kMaxDepth + 2; ++l) { st->lvl_first[l] = 0; st->lvl_count[l] = 0; }
+    for (int l = 0; l < kMaxDepth + 2; ++l) { st->lvl_first[l] = 0; st->lvl_count[l] = 0; st->done[2 * l] = 0; st->done[2 * l + 1] = 0; }
     st->lvl_first[0] = 0; st->lvl_count[0] = 1;
+    for (int k = 0; k < kMaxLevelNodes; ++k) st->best_key[k] = 0ull;
     na.begin[0] = 0; na.count[0] = n_rows;
     int b0 = 0, c0 = n_rows;
     plan->b_node[0] = 0; plan->b_sibling[0] = -1; plan->b_parent[0] = -1; plan->lvl_src[0] = 0;
@@ -100,6 +103,102 @@ __global__ void __launch_bounds__(128) scan_level_kernel(const int64_t* __restri
 __device__ __forceinline__ unsigned long long cand_key(float chg, int tiebreak) {
   return chg > 0.0f ? ((unsigned long long)__float_as_uint(chg) << 32) | (unsigned)tiebreak : 0ull;
 }
+struct FinishArgs {
+  int max_depth;
+  const float* cuts;
+  const float* min_vals;
+  TreeOut to;
+  LevelSegs* segs;
+  const int32_t* feat_pos;
+};
+struct FinishSmem { float chg[kMaxLevelNodes]; int feat[kMaxLevelNodes]; int child[kMaxLevelNodes]; };
+
+// runs in ONE CTA (any multiple of 32 threads) after every (node, feature) candidate of the level is
+// written; reads candidates with L2 loads because other CTAs of the same kernel produced them
+__device__ void level_finish_body(TreeState* st, int level, const FeatBest* feat_best, int f, const cb_tree_params& p,
+                                  NodeArrays na, const FinishArgs& fa, FinishSmem& sm, long long G0, long long H0) {
+  float* s_chg = sm.chg; int* s_feat = sm.feat; int* s_child = sm.child;
+  const int max_depth = fa.max_depth;
+  const float* cuts = fa.cuts; const float* min_vals = fa.min_vals;
+  TreeOut to = fa.to; LevelSegs* segs = fa.segs; const int32_t* feat_pos = fa.feat_pos;
+  const int first = st->lvl_first[level], cnt = st->lvl_count[level];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  if (level == 0 && threadIdx.x == 0) { na.G[0] = G0; na.H[0] = H0; }
+  __syncthreads();
+  const double ig = ldexp(1.0, -p.sg), ih = ldexp(1.0, -p.sh);
+  for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+    const unsigned long long key = __ldcg(&st->best_key[i]);
+    st->best_key[i] = 0ull;                                   // ready for the next level
+    const float bc = key ? __uint_as_float((unsigned)(key >> 32)) : 0.0f;
+    const int bf = key ? 0xFFFF - (int)(key & 0xFFFFu) : -1;
+    s_chg[i] = bc; s_feat[i] = bf;
+    bool valid = false;
+    if (bf >= 0) {
+      const long long HL = __ldcg(&feat_best[(size_t)i * f + bf].HL), HR = na.H[first + i] - HL;
+      valid = bc > 1e-6f && !(bc < p.gamma) && level < max_depth && HL != 0 && HR != 0;
+    }
+    s_child[i] = valid ? 1 : 0;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (level == 0) {
+      to.base_weight[0] = __double2float_rn(calc_weight(__dmul_rn((double)na.G[0], ig), __dmul_rn((double)na.H[0], ih), p));
+      to.sum_hess[0] = __double2float_rn(__dmul_rn((double)na.H[0], ih));
+    }
+    int next = st->n_nodes;
+    const int old = next;
+    for (int i = 0; i < cnt; ++i) {
+      if (s_child[i]) { s_child[i] = next; next += 2; } else s_child[i] = -1;
+    }
+    st->n_nodes = next;
+    st->lvl_first[level + 1] = old;
+    st->lvl_count[level + 1] = next - old;
+    segs->n = cnt;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+    const int nid = first + i;
+    segs->begin[i] = na.begin[nid];
+    segs->count[i] = na.count[nid];
+    segs->Lb[i] = 0; segs->nleft[i] = 0;
+    const int L = s_child[i];
+    if (L < 0) {
+      const float leaf = __fmul_rn(to.base_weight[nid], p.eta);
+      to.split_cond[nid] = leaf;
+      to.base_weight[nid] = leaf;
+      segs->kind[i] = 0; segs->leafL[i] = leaf; segs->leafR[i] = leaf;
+      segs->feat[i] = 0; segs->bin[i] = 0; segs->dl[i] = 0; segs->child[i] = -1;
+      continue;
+    }
+    const int R = L + 1, bf = s_feat[i];
+    const FeatBest* fbp = feat_best + (size_t)i * f + bf;
+    FeatBest fb;
+    fb.split_bin = __ldcg(&fbp->split_bin); fb.default_left = __ldcg(&fbp->default_left);
+    fb.GL = __ldcg(&fbp->GL); fb.HL = __ldcg(&fbp->HL);
+    const long long GL = fb.GL, HL = fb.HL, GR = na.G[nid] - GL, HR = na.H[nid] - HL;
+    to.left[nid] = L; to.right[nid] = R; to.parent[L] = nid; to.parent[R] = nid;
+    to.split_index[nid] = bf; to.split_bin[nid] = fb.split_bin;
+    to.split_cond[nid] = fb.split_bin >= 0 ? cuts[(size_t)bf * CB_CUT_STRIDE + fb.split_bin] : min_vals[bf];
+    to.default_left[nid] = (uint8_t)fb.default_left;
+    to.loss_chg[nid] = s_chg[i];
+    na.G[L] = GL; na.H[L] = HL; na.G[R] = GR; na.H[R] = HR;
+    const float bwL = __double2float_rn(calc_weight(__dmul_rn((double)GL, ig), __dmul_rn((double)HL, ih), p));
+    const float bwR = __double2float_rn(calc_weight(__dmul_rn((double)GR, ig), __dmul_rn((double)HR, ih), p));
+    to.sum_hess[L] = __double2float_rn(__dmul_rn((double)HL, ih));
+    to.sum_hess[R] = __double2float_rn(__dmul_rn((double)HR, ih));
+    segs->feat[i] = feat_pos[bf]; segs->bin[i] = fb.split_bin; segs->dl[i] = fb.default_left; segs->child[i] = L;
+    if (level + 1 == max_depth) {
+      const float lL = __fmul_rn(bwL, p.eta), lR = __fmul_rn(bwR, p.eta);
+      to.split_cond[L] = lL; to.base_weight[L] = lL;
+      to.split_cond[R] = lR; to.base_weight[R] = lR;
+      segs->kind[i] = 2; segs->leafL[i] = lL; segs->leafR[i] = lR;
+    } else {
+      to.base_weight[L] = bwL; to.base_weight[R] = bwR;
+      segs->kind[i] = 1; segs->leafL[i] = 0.0f; segs->leafR[i] = 0.0f;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __restrict__ level_buf,
                                                                int64_t* __restrict__ pool,
                                                                const HistPlan* __restrict__ plan,
@@ -108,27 +207,31 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
                                                                NodeArrays na, cb_tree_params p,
                                                                const uint8_t* __restrict__ feature_mask,
                                                                FeatBest* __restrict__ feat_best,
-                                                               const int64_t* __restrict__ tail) {
+                                                               const int64_t* __restrict__ tail, TreeState* stw,
+                                                               FinishArgs fa) {
   __shared__ long long sg[4], sh[4];
   __shared__ unsigned long long skf[4], skb[4];
+  __shared__ FinishSmem fsm;
+  __shared__ int s_last;
   const int i = blockIdx.y;
-  if (i >= st->lvl_count[level]) return;
+  const int cnt_level = st->lvl_count[level];
+  if (i >= cnt_level) return;
   const int feat = blockIdx.x;
   const int nid = st->lvl_first[level] + i;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   long long Gt, Ht;
   if (level == 0) {
     Gt = tail[0]; Ht = tail[1];
-    if (feat == 0 && tid == 0) { na.G[0] = Gt; na.H[0] = Ht; }
   } else {
     Gt = na.G[nid]; Ht = na.H[nid];
   }
+  do {
   if (feature_mask && !feature_mask[feat]) {
     if (tid == 0) {
       FeatBest fb; fb.chg = 0.0f; fb.split_bin = -1; fb.default_left = 0; fb.pad = 0; fb.GL = 0; fb.HL = 0;
       feat_best[(size_t)i * f + feat] = fb;
     }
-    return;
+    break;
   }
   const int b0 = __ldg(bin_ptr + feat), nb = __ldg(bin_ptr + feat + 1) - b0;
   const int src = plan->lvl_src[i], j = src >> 1;
@@ -210,7 +313,7 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
       FeatBest fb; fb.chg = 0.0f; fb.split_bin = -1; fb.default_left = 0; fb.pad = 0; fb.GL = 0; fb.HL = 0;
       feat_best[(size_t)i * f + feat] = fb;
     }
-    return;
+    break;
   }
   const int cbin = use_b ? (int)(kw & 0xFFFFu) : 0xFFFF - (int)(kw & 0xFFFFu);   // candidate bin
   const int sbin = use_b ? cbin - 1 : cbin;                                       // rows with code <= sbin go left
@@ -224,101 +327,26 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
     fb.chg = __uint_as_float((unsigned)(kw >> 32)); fb.split_bin = sbin; fb.default_left = use_b ? 1 : 0; fb.pad = 0;
     fb.GL = gl; fb.HL = hl;
     feat_best[(size_t)i * f + feat] = fb;
+    __threadfence();
+    atomicMax(&stw->best_key[i], ((kw >> 32) << 32) | (unsigned long long)(0xFFFF - feat));
+  }
+  } while (0);
+  // epilogue: the last CTA of the level to finish picks the splits and grows the tree (was a kernel of its own)
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    const unsigned prev = atomicAdd(&stw->done[2 * level], 1u);
+    s_last = prev == (unsigned)(gridDim.x * cnt_level) - 1u;
+  }
+  __syncthreads();
+  if (s_last) {
+    __threadfence();
+    level_finish_body(stw, level, feat_best, f, p, na, fa, fsm, Gt, Ht);
   }
 }
 
 // one block: pick each node's best feature, allocate children in node-id order (R9),
 // write the tree arrays, the children's totals and the level's segment table
-__global__ void __launch_bounds__(256) level_finish_kernel(TreeState* st, int level, int max_depth,
-                                                           const FeatBest* __restrict__ feat_best, int f,
-                                                           const float* __restrict__ cuts,
-                                                           const float* __restrict__ min_vals, cb_tree_params p,
-                                                           NodeArrays na, TreeOut to, LevelSegs* segs,
-                                                           const int32_t* __restrict__ feat_pos) {
-  __shared__ float s_chg[kMaxLevelNodes];
-  __shared__ int s_feat[kMaxLevelNodes];
-  __shared__ int s_child[kMaxLevelNodes];
-  const int first = st->lvl_first[level], cnt = st->lvl_count[level];
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const double ig = ldexp(1.0, -p.sg), ih = ldexp(1.0, -p.sh);
-  for (int i = wid; i < cnt; i += 8) {
-    float bc = 0.0f; int bf = -1;
-    for (int j = lane; j < f; j += 32) {
-      float c = feat_best[(size_t)i * f + j].chg;
-      if (c > bc) { bc = c; bf = j; }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {      // max chg, ties -> lower feature index
-      float oc = __shfl_xor_sync(0xffffffffu, bc, o);
-      int of = __shfl_xor_sync(0xffffffffu, bf, o);
-      if (oc > bc || (oc == bc && of >= 0 && (bf < 0 || of < bf))) { bc = oc; bf = of; }
-    }
-    if (lane == 0) {
-      s_chg[i] = bc; s_feat[i] = bf;
-      bool valid = false;
-      if (bf >= 0) {
-        const long long HL = feat_best[(size_t)i * f + bf].HL, HR = na.H[first + i] - HL;
-        valid = bc > 1e-6f && !(bc < p.gamma) && level < max_depth && HL != 0 && HR != 0;
-      }
-      s_child[i] = valid ? 1 : 0;
-    }
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    if (level == 0) {
-      to.base_weight[0] = __double2float_rn(calc_weight(__dmul_rn((double)na.G[0], ig), __dmul_rn((double)na.H[0], ih), p));
-      to.sum_hess[0] = __double2float_rn(__dmul_rn((double)na.H[0], ih));
-    }
-    int next = st->n_nodes;
-    const int old = next;
-    for (int i = 0; i < cnt; ++i) {
-      if (s_child[i]) { s_child[i] = next; next += 2; } else s_child[i] = -1;
-    }
-    st->n_nodes = next;
-    st->lvl_first[level + 1] = old;
-    st->lvl_count[level + 1] = next - old;
-    segs->n = cnt;
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
-    const int nid = first + i;
-    segs->begin[i] = na.begin[nid];
-    segs->count[i] = na.count[nid];
-    segs->Lb[i] = 0; segs->nleft[i] = 0;
-    const int L = s_child[i];
-    if (L < 0) {
-      const float leaf = __fmul_rn(to.base_weight[nid], p.eta);
-      to.split_cond[nid] = leaf;
-      to.base_weight[nid] = leaf;
-      segs->kind[i] = 0; segs->leafL[i] = leaf; segs->leafR[i] = leaf;
-      segs->feat[i] = 0; segs->bin[i] = 0; segs->dl[i] = 0; segs->child[i] = -1;
-      continue;
-    }
-    const int R = L + 1, bf = s_feat[i];
-    const FeatBest fb = feat_best[(size_t)i * f + bf];
-    const long long GL = fb.GL, HL = fb.HL, GR = na.G[nid] - GL, HR = na.H[nid] - HL;
-    to.left[nid] = L; to.right[nid] = R; to.parent[L] = nid; to.parent[R] = nid;
-    to.split_index[nid] = bf; to.split_bin[nid] = fb.split_bin;
-    to.split_cond[nid] = fb.split_bin >= 0 ? cuts[(size_t)bf * CB_CUT_STRIDE + fb.split_bin] : min_vals[bf];
-    to.default_left[nid] = (uint8_t)fb.default_left;
-    to.loss_chg[nid] = s_chg[i];
-    na.G[L] = GL; na.H[L] = HL; na.G[R] = GR; na.H[R] = HR;
-    const float bwL = __double2float_rn(calc_weight(__dmul_rn((double)GL, ig), __dmul_rn((double)HL, ih), p));
-    const float bwR = __double2float_rn(calc_weight(__dmul_rn((double)GR, ig), __dmul_rn((double)HR, ih), p));
-    to.sum_hess[L] = __double2float_rn(__dmul_rn((double)HL, ih));
-    to.sum_hess[R] = __double2float_rn(__dmul_rn((double)HR, ih));
-    segs->feat[i] = feat_pos[bf]; segs->bin[i] = fb.split_bin; segs->dl[i] = fb.default_left; segs->child[i] = L;
-    if (level + 1 == max_depth) {
-      const float lL = __fmul_rn(bwL, p.eta), lR = __fmul_rn(bwR, p.eta);
-      to.split_cond[L] = lL; to.base_weight[L] = lL;
-      to.split_cond[R] = lR; to.base_weight[R] = lR;
-      segs->kind[i] = 2; segs->leafL[i] = lL; segs->leafR[i] = lR;
-    } else {
-      to.base_weight[L] = bwL; to.base_weight[R] = bwR;
-      segs->kind[i] = 1; segs->leafL[i] = 0.0f; segs->leafR[i] = 0.0f;
-    }
-  }
-}
 
 // segment of a position: largest i with begin[i] <= pos, valid when pos < begin[i] + count[i]
 __device__ __forceinline__ int find_seg(const int* __restrict__ s_begin, const int* __restrict__ s_count, int n,
@@ -348,15 +376,122 @@ __device__ __forceinline__ int code_at(const BinsView& v, const uint8_t* __restr
   return __ldg(v.base + byte_index(v, row, pos));
 }
 
+// number of lefts strictly before position p (global prefix over all positions); L2 loads: the flag
+// words and tile prefixes were written by other CTAs of the same kernel
+__device__ __forceinline__ int lefts_before(const int* tile_ex, const uint32_t* flag_bits, int p, int n_rows) {
+  if (p <= 0) return 0;
+  int tile = p / kPartTile;
+  int w1 = p >> 5, part_bits = p & 31;
+  if (tile * kPartTile >= n_rows) {       // p == n_rows on a tile boundary: everything in the last tile
+    tile -= 1; w1 = (n_rows + 31) >> 5; part_bits = 0;
+  }
+  int s = __ldcg(tile_ex + tile);
+  for (int w = tile * (kPartTile / 32); w < w1; ++w) s += __popc(__ldcg(flag_bits + w));
+  if (part_bits && w1 * 32 < n_rows) s += __popc(__ldcg(flag_bits + w1) & ((1u << part_bits) - 1u));
+  return s;
+}
+
+// the same, computed by a whole warp (lanes stride over the tile's flag words)
+__device__ __forceinline__ int lefts_before_warp(const int* tile_ex, const uint32_t* flag_bits, int p, int n_rows, int lane) {
+  if (p <= 0) return 0;
+  int tile = p / kPartTile;
+  int w1 = p >> 5, part_bits = p & 31;
+  if (tile * kPartTile >= n_rows) { tile -= 1; w1 = (n_rows + 31) >> 5; part_bits = 0; }
+  int s = 0;
+  for (int w = tile * (kPartTile / 32) + lane; w < w1; w += 32) s += __popc(__ldcg(flag_bits + w));
+  if (lane == 0) {
+    s += __ldcg(tile_ex + tile);
+    if (part_bits && w1 * 32 < n_rows) s += __popc(__ldcg(flag_bits + w1) & ((1u << part_bits) - 1u));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  return s;
+}
+
+struct ScanSmem {
+  int warp_tot[32];
+  int pick[kMaxLevelNodes], cbegin[kMaxLevelNodes], ccount[kMaxLevelNodes];
+  int b_begin[kMaxBuild], b_count[kMaxBuild];
+};
+
+// P2, run by ONE CTA: exclusive scan of the tile counts, children segments, next level's histogram plan
+__device__ void part_scan_body(int* tile_cnt, int n_tiles, int n_rows, const uint32_t* flag_bits, LevelSegs* segs,
+                               TreeState* st, int level, int max_depth, NodeArrays na, HistPlan* plan, int grid,
+                               int by_hessian, ScanSmem& sm) {
+  const int nt = blockDim.x, lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarp = nt >> 5;
+  const int per = (n_tiles + nt - 1) / nt;
+  const int b = min(n_tiles, (int)threadIdx.x * per), e = min(n_tiles, b + per);
+  int s = 0;
+  for (int i = b; i < e; ++i) s += __ldcg(tile_cnt + i);
+  int inc = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
+  }
+  if (lane == 31) sm.warp_tot[wid] = inc;
+  __syncthreads();
+  int base = 0;
+  for (int w = 0; w < wid; ++w) base += sm.warp_tot[w];
+  int run = base + inc - s;
+  for (int i = b; i < e; ++i) { const int c = __ldcg(tile_cnt + i); tile_cnt[i] = run; run += c; }
+  __threadfence();
+  __syncthreads();
+  const int n = segs->n;
+  // one warp per split node: both boundary prefixes
+  for (int i = wid; i < n; i += nwarp) {
+    if (segs->kind[i] != 1) { if (lane == 0) sm.pick[i] = -1; continue; }
+    const int bg = segs->begin[i], ct = segs->count[i];
+    const int Lb = lefts_before_warp(tile_cnt, flag_bits, bg, n_rows, lane);
+    const int Le = lefts_before_warp(tile_cnt, flag_bits, bg + ct, n_rows, lane);
+    if (lane == 0) {
+      const int nl = Le - Lb;
+      segs->Lb[i] = Lb; segs->nleft[i] = nl;
+      const int L = segs->child[i];
+      na.begin[L] = bg; na.count[L] = nl;
+      na.begin[L + 1] = bg + nl; na.count[L + 1] = ct - nl;
+      int pick = -1;
+      if (level + 1 < max_depth) {
+        const bool left_small = by_hessian ? (na.H[L] <= na.H[L + 1]) : (nl <= ct - nl);
+        pick = (L << 1) | (left_small ? 0 : 1);
+        sm.cbegin[i] = left_small ? bg : bg + nl;
+        sm.ccount[i] = left_small ? nl : ct - nl;
+      }
+      sm.pick[i] = pick;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int nb = 0;
+    const int first = st->lvl_first[level], first_next = st->lvl_first[level + 1];
+    for (int i = 0; i < n; ++i) {
+      if (sm.pick[i] < 0) continue;
+      const int L = sm.pick[i] >> 1, R = L + 1;
+      const bool left_small = (sm.pick[i] & 1) == 0;
+      plan->b_node[nb] = left_small ? L : R; plan->b_sibling[nb] = left_small ? R : L; plan->b_parent[nb] = first + i;
+      plan->lvl_src[L - first_next] = 2 * nb + (left_small ? 0 : 1);
+      plan->lvl_src[R - first_next] = 2 * nb + (left_small ? 1 : 0);
+      sm.b_begin[nb] = sm.cbegin[i];
+      sm.b_count[nb] = sm.ccount[i];
+      ++nb;
+    }
+    plan_ctas(plan, nb, sm.b_begin, sm.b_count, grid);
+  }
+}
+
 // P1: go-left flags of every position that sits in a node being split (kind 1)
 __global__ void __launch_bounds__(256) part_level_flags_kernel(BinsView view, const uint8_t* __restrict__ bins_cm,
                                                                const uint32_t* __restrict__ rows_in, int identity,
                                                                int n_rows, const LevelSegs* __restrict__ segs,
                                                                uint32_t* __restrict__ flag_bits,
-                                                               int* __restrict__ tile_cnt) {
+                                                               int* __restrict__ tile_cnt, LevelSegs* segs_w,
+                                                               TreeState* st, int level, int max_depth, NodeArrays na,
+                                                               HistPlan* plan, int grid, int by_hessian) {
   __shared__ SegCache sc;
   __shared__ SegSplit ss;
+  __shared__ ScanSmem scan_sm;
   __shared__ int wsum[8];
+  __shared__ int s_last;
   const int n = segs->n;
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
     sc.begin[i] = segs->begin[i]; sc.count[i] = segs->count[i];
@@ -403,98 +538,18 @@ __global__ void __launch_bounds__(256) part_level_flags_kernel(BinsView view, co
     int t = 0;
     for (int k = 0; k < 8; ++k) t += wsum[k];
     tile_cnt[blockIdx.x] = t;
+    __threadfence();
+    const unsigned prev = atomicAdd(&st->done[2 * level + 1], 1u);
+    s_last = prev == gridDim.x - 1u;
+  }
+  __syncthreads();
+  if (s_last) {            // the last tile to finish runs the scan + planning step (was a kernel of its own)
+    __threadfence();
+    part_scan_body(tile_cnt, (int)gridDim.x, n_rows, flag_bits, segs_w, st, level, max_depth, na, plan, grid, by_hessian,
+                   scan_sm);
   }
 }
 
-// number of lefts strictly before position p (global prefix over all positions)
-__device__ __forceinline__ int lefts_before(const int* __restrict__ tile_ex, const uint32_t* __restrict__ flag_bits,
-                                            int p, int n_rows) {
-  if (p <= 0) return 0;
-  const int tile = p / kPartTile;
-  if (tile * kPartTile >= n_rows) {       // p == n_rows on a tile boundary: everything before
-    int t = tile - 1;
-    int s = tile_ex[t];
-    for (int w = t * (kPartTile / 32); w * 32 < n_rows; ++w) s += __popc(flag_bits[w]);
-    return s;
-  }
-  int s = tile_ex[tile];
-  const int w0 = tile * (kPartTile / 32), w1 = p >> 5;
-  for (int w = w0; w < w1; ++w) s += __popc(flag_bits[w]);
-  if ((p & 31) && w1 * 32 < n_rows) s += __popc(flag_bits[w1] & ((1u << (p & 31)) - 1u));
-  return s;
-}
-
-// P2 (one block): scan tile counts, place the children segments, plan the next level's histograms
-__global__ void __launch_bounds__(1024) part_level_scan_kernel(int* __restrict__ tile_cnt, int n_tiles, int n_rows,
-                                                               const uint32_t* __restrict__ flag_bits,
-                                                               LevelSegs* segs, TreeState* st, int level,
-                                                               int max_depth, NodeArrays na, HistPlan* plan, int grid,
-                                                               int by_hessian) {
-  __shared__ int part[1024];
-  __shared__ int b_begin[kMaxBuild], b_count[kMaxBuild];
-  const int per = (n_tiles + 1023) / 1024;
-  const int b = threadIdx.x * per, e = min(n_tiles, b + per);
-  int s = 0;
-  for (int i = b; i < e; ++i) s += tile_cnt[i];
-  part[threadIdx.x] = s;
-  __syncthreads();
-  for (int o = 1; o < 1024; o <<= 1) {
-    int v = threadIdx.x >= o ? part[threadIdx.x - o] : 0;
-    __syncthreads();
-    part[threadIdx.x] += v;
-    __syncthreads();
-  }
-  int run = part[threadIdx.x] - s;
-  for (int i = b; i < e; ++i) { int c = tile_cnt[i]; tile_cnt[i] = run; run += c; }
-  __threadfence_block();
-  __syncthreads();
-  const int n = segs->n;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    if (segs->kind[i] != 1) continue;
-    const int bg = segs->begin[i], ct = segs->count[i];
-    const int Lb = lefts_before(tile_cnt, flag_bits, bg, n_rows);
-    const int Le = lefts_before(tile_cnt, flag_bits, bg + ct, n_rows);
-    const int nl = Le - Lb;
-    segs->Lb[i] = Lb; segs->nleft[i] = nl;
-    const int L = segs->child[i];
-    na.begin[L] = bg; na.count[L] = nl;
-    na.begin[L + 1] = bg + nl; na.count[L + 1] = ct - nl;
-  }
-  __syncthreads();
-  // next level's histogram plan: per split node pick the child to build (parallel), then one thread
-  // numbers the build slots and hands out CTAs (reads shared memory only)
-  __shared__ int b_pick[kMaxLevelNodes];
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    int pick = -1;
-    if (level + 1 < max_depth && segs->kind[i] == 1) {
-      const int L = segs->child[i], R = L + 1;
-      const bool left_small = by_hessian ? (na.H[L] <= na.H[R]) : (na.count[L] <= na.count[R]);
-      pick = left_small ? 0 : 1;
-      part[i] = na.begin[left_small ? L : R];          // reuse the scan scratch: begin of the built child
-      part[kMaxLevelNodes + i] = na.count[left_small ? L : R];
-      b_pick[i] = (L << 1) | pick;
-    }
-    if (pick < 0) b_pick[i] = -1;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int nb = 0;
-    const int first = st->lvl_first[level], first_next = st->lvl_first[level + 1];
-    for (int i = 0; i < n; ++i) {
-      if (b_pick[i] < 0) continue;
-      const int L = b_pick[i] >> 1, R = L + 1;
-      const bool left_small = (b_pick[i] & 1) == 0;
-      const int bn = left_small ? L : R;
-      plan->b_node[nb] = bn; plan->b_sibling[nb] = left_small ? R : L; plan->b_parent[nb] = first + i;
-      plan->lvl_src[L - first_next] = 2 * nb + (left_small ? 0 : 1);
-      plan->lvl_src[R - first_next] = 2 * nb + (left_small ? 1 : 0);
-      b_begin[nb] = part[i];
-      b_count[nb] = part[kMaxLevelNodes + i];
-      ++nb;
-    }
-    plan_ctas(plan, nb, b_begin, b_count, grid);
-  }
-}
 
 // P3: stable scatter of split nodes (lefts first), leaf values of nodes that stopped here
 __global__ void __launch_bounds__(256) part_level_scatter_kernel(const uint32_t* __restrict__ rows_in, int identity,
