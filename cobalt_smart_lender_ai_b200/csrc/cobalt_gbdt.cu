@@ -450,6 +450,7 @@ struct cb_trainer_s {
   bool identity;
   uint32_t* flag_bits;
   int* tile_cnt;
+  int* group_cnt;
   TreeState* st;
   LevelSegs* segs;
   HistPlan* plan;
@@ -488,6 +489,7 @@ static int trainer_layout(const cb_train_config* cfg, const DeviceInfo& di, void
   uint32_t* r1 = b.take<uint32_t>((size_t)n);
   uint32_t* flag_bits = b.take<uint32_t>((size_t)(n / 32 + 2));
   int* tile_cnt = b.take<int>((size_t)(n / kPartTile + 2));
+  int* group_cnt = b.take<int>((size_t)(n / kPartTile / kTileGroup + 2));
   TreeState* st = b.take<TreeState>(1);
   LevelSegs* segs = b.take<LevelSegs>(1);
   HistPlan* plan = b.take<HistPlan>(1);
@@ -511,6 +513,7 @@ static int trainer_layout(const cb_train_config* cfg, const DeviceInfo& di, void
   if (t) {
     t->max_nodes = max_nodes; t->S = S; t->S2 = 2 * S; t->pool_slots = pool_slots; t->lb_slots = lb_slots;
     t->gpair = gpair; t->rows[0] = r0; t->rows[1] = r1; t->flag_bits = flag_bits; t->tile_cnt = tile_cnt;
+    t->group_cnt = group_cnt;
     t->st = st; t->segs = segs; t->plan = plan; t->na = na; t->pool = pool; t->level_buf = level_buf;
     t->partials = partials; t->feat_best = feat_best;
     t->cf_lay = cf_lay; t->cf_slot_of = cf_slot_of; t->cf_fold_src = cf_fold_src; t->cf_fold_dst = cf_fold_dst;
@@ -726,26 +729,32 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   const int nb = level == 0 ? 1 : (1 << (level - 1));
   const int ln = 1 << level;
   const int n = (int)t->cfg.n_rows;
-  FinishArgs fa;
-  fa.max_depth = D; fa.cuts = t->buf.cuts; fa.min_vals = t->buf.min_vals; fa.to = tree_out(t); fa.segs = t->segs;
-  fa.feat_pos = t->feat_pos;
+  const int n_groups = ceil_div(t->n_part_tiles, kTileGroup);
   scan_level_fused_kernel<<<dim3(t->cfg.n_features, ln), 128, 0, s>>>(
       t->level_buf, t->pool, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S, t->st, level, t->na, t->cfg.tree, t->fmask,
-      t->feat_best, level == 0 ? t->level_buf + t->S2 : nullptr, t->st, fa);
+      t->feat_best, level == 0 ? t->level_buf + t->S2 : nullptr, t->st, t->group_cnt, n_groups);
   t->launches += 1;
+  LevelCtx lc;
+  lc.st = t->st; lc.level = level; lc.max_depth = D; lc.f = t->cfg.n_features; lc.feat_best = t->feat_best;
+  lc.p = t->cfg.tree; lc.na = t->na; lc.feat_pos = t->feat_pos;
+  const BinsView view = make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked);
   const uint32_t* rin = t->rows[t->cur];
   const int ident = t->identity ? 1 : 0;
   if (level + 1 < D) {
     uint32_t* rout = t->rows[t->cur ^ 1];
-    part_level_flags_kernel<<<t->n_part_tiles, 256, 0, s>>>(
-        make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked), t->buf.bins_cm, rin, ident, n, t->segs,
-        t->flag_bits, t->tile_cnt, t->segs, t->st, level, D, t->na, t->plan, t->grid, t->cfg.world_size > 1 ? 1 : 0);
-    part_level_scatter_kernel<<<t->n_part_tiles, 256, 0, s>>>(rin, ident, n, t->segs, t->flag_bits, t->tile_cnt, rout,
-                                                              t->buf.margin);
+    part_level_flags_kernel<<<t->n_part_tiles + 1, 256, 0, s>>>(view, t->buf.bins_cm, rin, ident, n, t->n_part_tiles, lc, t->st,
+                                                                t->buf.cuts, t->buf.min_vals, tree_out(t), t->segs,
+                                                                t->flag_bits, t->tile_cnt, t->group_cnt);
+    part_level_scatter_kernel<<<t->n_part_tiles + 1, 256, 0, s>>>(rin, ident, n, t->n_part_tiles, t->segs, t->flag_bits,
+                                                                  t->tile_cnt, t->group_cnt, rout, t->buf.margin, t->st,
+                                                                  level, D, t->na, t->plan, t->grid,
+                                                                  t->cfg.world_size > 1 ? 1 : 0);
     t->cur ^= 1; t->identity = false;
     t->launches += 2;
   } else {
-    final_apply_kernel<<<ceil_div(n, 256), 256, 0, s>>>(make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked), t->buf.bins_cm, rin, ident, n, t->segs, t->buf.margin);
+    const int nblk = ceil_div(n, 256);
+    final_apply_kernel<<<nblk + 1, 256, 0, s>>>(view, t->buf.bins_cm, rin, ident, n, nblk, lc, t->st, t->buf.cuts,
+                                                t->buf.min_vals, tree_out(t), t->segs, t->buf.margin);
     t->launches += 1;
   }
   CB_LAUNCH_CHECK();
@@ -754,7 +763,7 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
 
 int cb_trainer_round_end(cb_trainer* t, void* stream) {
   if (!t) return fail(CB_ERR_INVALID, "trainer: null handle");
-  round_end_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(t->st, t->buf.n_nodes + t->tree_index);
+  round_end_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(t->st, t->buf.n_nodes + t->tree_index);
   CB_LAUNCH_CHECK();
   t->launches += 1;
   return CB_OK;
