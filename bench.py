@@ -22,6 +22,7 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+_OUT = sys.stdout
 
 N_ROWS, N_FEAT, DEPTH, ROUNDS_CFG, ETA = 2_200_000, 150, 6, 500, 0.3
 SCORE_ROWS, SCORE_TREES = 10_000_000, 1000
@@ -270,7 +271,7 @@ def run_ours(args):
         visits = args.score_rows * SCORE_TREES * DEPTH
         sc = {"metric": "scoring rows/s", "value": round(rows_s, 0), "ms_per_pass": round(ms_s, 3),
               "workload": f"{args.score_rows} rows x {N_FEAT}, {SCORE_TREES} trees depth {DEPTH} (configs[4])",
-              "roofline": {"kernel": "predict_kernel", "bound": "hbm", "achieved": round(sbytes / (ms_s / 1e3) / 1e9, 1),
+              "roofline": {"kernel": "predict_heap_kernel", "bound": "hbm (contract); binding resource is shared-memory lookups + ALU issue", "achieved": round(sbytes / (ms_s / 1e3) / 1e9, 1),
                            "peak": peak, "unit": "GB/s", "frac": round(sbytes / (ms_s / 1e3) / 1e9 / peak, 4),
                            "traffic": None},
               "node_visits_per_s": round(visits / (ms_s / 1e3), 0)}
@@ -321,7 +322,7 @@ def run_ours(args):
                                                 "parallelism": f"rows sharded x{world}, NCCL allreduce of per-level histograms"},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clk.summary(), "scoring": scoring, "prep_ms": round(t_prep, 2), "train_auc_200k": auc}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_OUT, flush=True)
     if world > 1:
         torch.distributed.destroy_process_group()
 
@@ -366,10 +367,21 @@ def run_reference(args):
             "cpu_baseline": {"value": round(val, 3), "unit": "rounds/s", "cores": O.num_threads(), "kind": "port", "sample": sample},
             "e2e": {"value": round(val, 3), "unit": "rounds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "raw_rounds_per_s_on_sample": round(args.steps / dt, 3), "prep_seconds": round(t_prep, 2)}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_OUT, flush=True)
+
+
+def _quiet_stdout():
+    """Libraries (NCCL prints its version) may write to fd 1; the contract is ONE JSON line on stdout.
+    Point fd 1 at stderr for the run and return a writer on the original stdout."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    return os.fdopen(saved, "w")
 
 
 def main():
+    global _OUT
+    _OUT = _quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)

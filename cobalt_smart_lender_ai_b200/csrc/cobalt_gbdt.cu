@@ -127,7 +127,7 @@ int cb_grad_logistic_q(const float* margin, const uint8_t* y, const float* weigh
   grad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(margin, y, weight, n, spw, ldexpf(1.0f, sg), ldexpf(1.0f, sh),
                                                       keep_thresh, seed, tree, row_offset,
                                                       reinterpret_cast<int2*>(gpair),
-                                                      reinterpret_cast<unsigned long long*>(totals));
+                                                      reinterpret_cast<unsigned long long*>(totals), nullptr);
   CB_LAUNCH_CHECK();
   return CB_OK;
 }
@@ -572,6 +572,7 @@ int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, v
   t->n_part_tiles = ceil_div(cfg->n_rows, kPartTile);
   t->cur = 0; t->identity = true; t->tree_index = 0; t->fmask = nullptr; t->launches = 0; t->timing = false;
   plan_tiles_kernel<<<1, 1>>>(buf->bin_ptr, cfg->n_features, budget, t->plan);
+  set_tree_index_kernel<<<1, 1>>>(t->st, 0);
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { delete t; return fail(CB_ERR_CUDA, "cb_trainer_create: %s", cudaGetErrorString(e)); }
   // column placement -> conflict-free shared-memory tables (host side, one-off)
@@ -644,7 +645,7 @@ int cb_trainer_last_hist_timing_sync(cb_trainer* t, float* ms_accum, float* ms_r
 }
 
 static TreeOut tree_out(cb_trainer_s* t) {
-  const size_t o = (size_t)t->tree_index * t->max_nodes;
+  const size_t o = 0;   // row 0: kernels add the device-side tree index
   TreeOut to;
   to.left = t->buf.left + o; to.right = t->buf.right + o; to.parent = t->buf.parent + o;
   to.split_index = t->buf.split_index + o; to.split_bin = t->buf.split_bin + o; to.split_cond = t->buf.split_cond + o;
@@ -653,18 +654,22 @@ static TreeOut tree_out(cb_trainer_s* t) {
   return to;
 }
 
-int cb_trainer_round_begin(cb_trainer* t, int tree_index, const uint8_t* feature_mask, void* stream) {
+int cb_trainer_round_begin(cb_trainer* t, int tree_index, const uint8_t* feature_masks, void* stream) {
   if (!t) return fail(CB_ERR_INVALID, "trainer: null handle");
-  if (tree_index < 0 || tree_index >= t->cfg.max_trees) return fail(CB_ERR_INVALID, "trainer: tree_index %d out of range", tree_index);
+  if (tree_index >= t->cfg.max_trees) return fail(CB_ERR_INVALID, "trainer: tree_index %d out of range", tree_index);
   cudaStream_t s = (cudaStream_t)stream;
-  t->tree_index = tree_index; t->fmask = feature_mask; t->identity = true; t->cur = 0;
+  t->fmask = feature_masks; t->identity = true; t->cur = 0;
   const int64_t n = t->cfg.n_rows;
+  if (tree_index >= 0) {                 // negative: keep the device-side counter (CUDA-graph replay)
+    set_tree_index_kernel<<<1, 1, 0, s>>>(t->st, tree_index);
+    t->launches += 1;
+  }
   CB_CUDA(cudaMemsetAsync(t->st->root_tot, 0, 2 * sizeof(long long), s));
   int g = (int)std::min<int64_t>(ceil_div(n, 256), (int64_t)t->di.sm_count * 8);
   grad_kernel<<<g, 256, 0, s>>>(t->buf.margin, t->buf.y, t->buf.weight, n, t->cfg.scale_pos_weight,
                                 ldexpf(1.0f, t->cfg.tree.sg), ldexpf(1.0f, t->cfg.tree.sh), t->cfg.keep_thresh,
-                                t->cfg.seed, (uint32_t)tree_index, t->cfg.row_offset, t->gpair,
-                                reinterpret_cast<unsigned long long*>(t->st->root_tot));
+                                t->cfg.seed, 0u, t->cfg.row_offset, t->gpair,
+                                reinterpret_cast<unsigned long long*>(t->st->root_tot), &t->st->tree_index);
   round_init_kernel<<<ceil_div(t->max_nodes, 256), 256, 0, s>>>(t->st, t->na, tree_out(t), t->max_nodes, (int)n,
                                                                 t->plan, t->grid);
   CB_LAUNCH_CHECK();
@@ -763,7 +768,7 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
 
 int cb_trainer_round_end(cb_trainer* t, void* stream) {
   if (!t) return fail(CB_ERR_INVALID, "trainer: null handle");
-  round_end_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(t->st, t->buf.n_nodes + t->tree_index);
+  round_end_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(t->st, t->buf.n_nodes);
   CB_LAUNCH_CHECK();
   t->launches += 1;
   return CB_OK;

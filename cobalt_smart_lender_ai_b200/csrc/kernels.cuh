@@ -88,7 +88,9 @@ __global__ void __launch_bounds__(256) grad_kernel(const float* __restrict__ mar
                                                    const float* __restrict__ weight, int64_t n, float spw,
                                                    float fg, float fh, uint32_t keep_thresh, uint32_t seed,
                                                    uint32_t tree, int64_t row_offset, int2* __restrict__ gpair,
-                                                   unsigned long long* __restrict__ totals) {
+                                                   unsigned long long* __restrict__ totals,
+                                                   const int* __restrict__ tree_ptr) {
+  if (tree_ptr) tree = (uint32_t)*tree_ptr;          // trainer: the device-side round counter
   int64_t G = 0, H = 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float p = spec_sigmoid(__ldg(margin + i));

@@ -11,7 +11,7 @@ struct TreeState {                        // device memory
   int n_nodes;
   int lvl_first[kMaxDepth + 2];
   int lvl_count[kMaxDepth + 2];
-  int pad_;
+  int tree_index;                         // forest row being grown; advanced by round_end (graph replay needs no host value)
   long long root_tot[2];                  // local sum of (q_g, q_h), filled by the gradient kernel
   unsigned long long best_key[kMaxLevelNodes];  // per level node: max over features of (chg bits << 32 | 0xFFFF - feature)
 };
@@ -34,8 +34,21 @@ struct TreeOut {                          // slices of the forest arrays for the
   float* split_cond; uint8_t* default_left; float* base_weight; float* loss_chg; float* sum_hess;
 };
 
-__global__ void round_init_kernel(TreeState* st, NodeArrays na, TreeOut to, int max_nodes, int n_rows,
+// `base` points at forest row 0; the row of the tree being grown comes from the device-side counter
+__device__ __forceinline__ TreeOut tree_slice(const TreeOut& base, const TreeState* st, int max_nodes) {
+  const size_t o = (size_t)st->tree_index * max_nodes;
+  TreeOut t;
+  t.left = base.left + o; t.right = base.right + o; t.parent = base.parent + o; t.split_index = base.split_index + o;
+  t.split_bin = base.split_bin + o; t.split_cond = base.split_cond + o; t.default_left = base.default_left + o;
+  t.base_weight = base.base_weight + o; t.loss_chg = base.loss_chg + o; t.sum_hess = base.sum_hess + o;
+  return t;
+}
+
+__global__ void set_tree_index_kernel(TreeState* st, int idx) { st->tree_index = idx; }
+
+__global__ void round_init_kernel(TreeState* st, NodeArrays na, TreeOut to_base, int max_nodes, int n_rows,
                                   HistPlan* plan, int grid) {
+  const TreeOut to = tree_slice(to_base, st, max_nodes);
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < max_nodes) {
     to.left[i] = -1; to.right[i] = -1; to.parent[i] = 2147483647; to.split_index[i] = 0; to.split_bin[i] = 0;
@@ -94,7 +107,7 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
     Gt = na.G[nid]; Ht = na.H[nid];
   }
   do {
-  if (feature_mask && !feature_mask[feat]) {
+  if (feature_mask && !feature_mask[(size_t)st->tree_index * f + feat]) {
     if (tid == 0) {
       FeatBest fb; fb.chg = 0.0f; fb.split_bin = -1; fb.default_left = 0; fb.pad = 0; fb.GL = 0; fb.HL = 0;
       feat_best[(size_t)i * f + feat] = fb;
@@ -388,7 +401,7 @@ __global__ void __launch_bounds__(256) part_level_flags_kernel(BinsView view, co
   __shared__ NodeTable nt;
   __shared__ int wsum[8];
   if (blockIdx.x == 0) {                            // the extra CTA (scheduled first): serial bookkeeping, overlapped with the tiles
-    finish_level(stw, c, cuts, min_vals, to, segs, nt.begin);
+    finish_level(stw, c, cuts, min_vals, tree_slice(to, stw, (1 << (c.max_depth + 1)) - 1), segs, nt.begin);
     return;
   }
   const int tile = (int)blockIdx.x - 1;
@@ -604,7 +617,7 @@ __global__ void __launch_bounds__(256) final_apply_kernel(BinsView view, const u
                                                           float* __restrict__ margin) {
   __shared__ NodeTable nt;
   if (blockIdx.x == 0) {
-    finish_level(stw, c, cuts, min_vals, to, segs, nt.begin);
+    finish_level(stw, c, cuts, min_vals, tree_slice(to, stw, (1 << (c.max_depth + 1)) - 1), segs, nt.begin);
     return;
   }
   build_node_table(nt, c, true);
@@ -624,9 +637,12 @@ __global__ void __launch_bounds__(256) final_apply_kernel(BinsView view, const u
   margin[row] = __fadd_rn(margin[row], leaf);
 }
 
-__global__ void round_end_kernel(TreeState* st, int32_t* n_nodes_out) {
-  *n_nodes_out = st->n_nodes;
+__global__ void round_end_kernel(TreeState* st, int32_t* n_nodes_all) {
   for (int i = threadIdx.x; i < kMaxLevelNodes; i += blockDim.x) st->best_key[i] = 0ull;
+  if (threadIdx.x == 0) {
+    n_nodes_all[st->tree_index] = st->n_nodes;
+    st->tree_index += 1;
+  }
 }
 
 }  // namespace cb

@@ -44,7 +44,7 @@ def colsample_masks(n_trees: int, n_features: int, colsample: float, seed: int) 
     if colsample >= 1.0:
         return None
     k = max(1, int(colsample * n_features))
-    masks = np.zeros((n_trees, n_features), np.uint8)
+    masks = np.zeros((n_trees, n_features), np.uint8)  # row t masks tree t
     for t in range(n_trees):
         keys = [(_hash32(seed ^ 0x5bd1e995, t, j), j) for j in range(n_features)]
         keys.sort()

@@ -10,6 +10,7 @@ level -- the path's one collective.
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -70,6 +71,10 @@ class GpuTrainer:
         self.handle = h
         self.n_trees = 0
         self._level_views = {}
+        self._graphs = {}
+        self._graph_launches = 0
+        self._launches_per_round = 0
+        self.graph_error = None
 
     def close(self):
         if getattr(self, "handle", None):
@@ -92,28 +97,79 @@ class GpuTrainer:
             self._level_views[level] = v
         return v
 
-    def boost_one(self, feature_mask: torch.Tensor | None = None) -> None:
-        if self.n_trees >= self.max_trees:
-            raise _lib.CobaltError("forest capacity exhausted")
+    def _enqueue_round(self, tree_index: int, feature_masks: torch.Tensor | None) -> None:
+        """One boosting round on the current stream.  tree_index < 0 continues the device-side counter."""
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        fm = None if feature_mask is None else C.c_void_p(feature_mask.data_ptr())
+        fm = None if feature_masks is None else C.c_void_p(feature_masks.data_ptr())
         if self.world == 1:
-            check(self.lib.cb_trainer_boost_round(self.handle, self.n_trees, fm, st))
+            check(self.lib.cb_trainer_boost_round(self.handle, tree_index, fm, st))
         else:
-            check(self.lib.cb_trainer_round_begin(self.handle, self.n_trees, fm, st))
+            check(self.lib.cb_trainer_round_begin(self.handle, tree_index, fm, st))
             for level in range(self.max_depth):
                 check(self.lib.cb_trainer_level_hist(self.handle, level, st))
                 torch.distributed.all_reduce(self._level_view(level), group=self.group)
                 check(self.lib.cb_trainer_level_split(self.handle, level, st))
             check(self.lib.cb_trainer_round_end(self.handle, st))
+
+    def boost_one(self, feature_masks: torch.Tensor | None = None) -> None:
+        """feature_masks: u8 [max_trees, f] on the device (row t masks tree t) or None."""
+        if self.n_trees >= self.max_trees:
+            raise _lib.CobaltError("forest capacity exhausted")
+        self._enqueue_round(self.n_trees, feature_masks)
         self.n_trees += 1
 
-    def boost(self, n_rounds: int, feature_masks: torch.Tensor | None = None) -> None:
-        for t in range(n_rounds):
-            self.boost_one(None if feature_masks is None else feature_masks[self.n_trees])
+    def boost(self, n_rounds: int, feature_masks: torch.Tensor | None = None, use_graph: bool | None = None) -> None:
+        """n_rounds boosting rounds.  From the second round on, a CUDA graph of one round (kernels and,
+        when sharded, the NCCL all-reduces) is replayed: the launch sequence of a round is fixed and
+        the forest row comes from a device-side counter, so no host work remains per round."""
+        if self.n_trees + n_rounds > self.max_trees:
+            raise _lib.CobaltError("forest capacity exhausted")
+        if feature_masks is not None:
+            assert feature_masks.dtype == torch.uint8 and feature_masks.shape == (self.max_trees, self.f)
+        if use_graph is None:
+            use_graph = os.environ.get("COBALT_CUDA_GRAPH", "1") != "0"
+        done = 0
+        if use_graph and n_rounds >= 4:
+            self.boost_one(feature_masks)          # eager: warms up NCCL and fixes the counter
+            done = 1
+            graph = self._capture_round(feature_masks)
+            if graph is not None:
+                for _ in range(n_rounds - 1):
+                    graph.replay()
+                self.n_trees += n_rounds - 1
+                self._graph_launches += self._launches_per_round * (n_rounds - 1)
+                done = n_rounds
+        for _ in range(n_rounds - done):
+            self.boost_one(feature_masks)
+
+    def _capture_round(self, feature_masks):
+        key = None if feature_masks is None else feature_masks.data_ptr()
+        if key in self._graphs:
+            return self._graphs[key]
+        graph = None
+        try:
+            l0 = self.launch_count_raw()
+            g = torch.cuda.CUDAGraph()
+            side = torch.cuda.Stream(device=self.dev)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+                self._enqueue_round(-1, feature_masks)
+            torch.cuda.current_stream().wait_stream(side)
+            self._launches_per_round = self.launch_count_raw() - l0
+            self._graph_launches -= self._launches_per_round      # the capture pass launched nothing
+            graph = g
+        except Exception as e:  # capture unsupported (e.g. the collective): stay eager, loudly
+            self.graph_error = repr(e)
+            torch.cuda.synchronize()
+        self._graphs[key] = graph
+        return graph
+
+    def launch_count_raw(self) -> int:
+        return int(self.lib.cb_trainer_launch_count(self.handle))
 
     def launch_count(self) -> int:
-        return int(self.lib.cb_trainer_launch_count(self.handle))
+        """Kernels launched so far, counting graph replays."""
+        return self.launch_count_raw() + self._graph_launches
 
     def row_order(self) -> torch.Tensor | None:
         ptr = C.c_void_p()

@@ -206,11 +206,14 @@ int cb_trainer_workspace_bytes(const cb_train_config* cfg, size_t* bytes);
 int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, void* workspace,
                       size_t workspace_bytes, cb_trainer** out);
 void cb_trainer_destroy(cb_trainer* tr);
-/* whole round on one GPU; feature_mask: u8 [f] (device) or NULL (colsample_bytree) */
-int cb_trainer_boost_round(cb_trainer* tr, int tree_index, const uint8_t* feature_mask, void* stream);
+/* whole round on one GPU.  feature_masks: u8 [max_trees][f] (device; row t masks tree t) or NULL
+ * (colsample_bytree).  tree_index >= 0 selects the forest row; tree_index < 0 continues from the
+ * device-side counter that every round_end advances, so one captured CUDA graph of a round can be
+ * replayed round after round without any host value changing. */
+int cb_trainer_boost_round(cb_trainer* tr, int tree_index, const uint8_t* feature_masks, void* stream);
 /* the same round in steps, for row-sharded training:
  *   round_begin; for level in 0..max_depth-1: level_hist, <allreduce level buffer>, level_split; round_end */
-int cb_trainer_round_begin(cb_trainer* tr, int tree_index, const uint8_t* feature_mask, void* stream);
+int cb_trainer_round_begin(cb_trainer* tr, int tree_index, const uint8_t* feature_masks, void* stream);
 int cb_trainer_level_hist(cb_trainer* tr, int level, void* stream);
 int cb_trainer_level_split(cb_trainer* tr, int level, void* stream);
 int cb_trainer_round_end(cb_trainer* tr, void* stream);
