@@ -186,8 +186,14 @@ def run_ours(args):
     torch.cuda.synchronize()
     lib.cb_trainer_enable_timing(tr.handle, 0)
     achieved = alg_bytes / (acc_ms / 1e3) / 1e9
+    traffic = None
+    try:      # per-launch DRAM bytes of the same kernel from the committed ncu --set full capture
+        with open(os.path.join(ROOT, "profiles", "r01_roofline.json")) as fh:
+            traffic = int(json.load(fh)["dram_bytes_per_launch_mean"]) if world == 1 else None
+    except Exception:
+        pass
     roofline = {"kernel": "hist_accum_cf_kernel" if cf_flag else "hist_accum_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
-                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                 "avg_launch_ms": round(acc_ms / n_launch, 4), "launches_timed": n_launch,
                 "alg_bytes_per_launch": int(alg_bytes / n_launch), "hist_reduce_ms_per_launch": round(red_ms / n_launch, 4),
                 "hist_share_of_round": round((acc_ms + red_ms) / 3 / (ms / args.steps), 3)}
