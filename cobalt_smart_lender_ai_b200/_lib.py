@@ -112,6 +112,8 @@ _SIGS = {
     "cb_trainer_row_order": (C.c_int, [_VP, C.POINTER(_VP)]),
     "cb_trainer_node_hist": (C.c_int, [_VP, _I, C.POINTER(_VP)]),
     "cb_trainer_launch_count": (C.c_int64, [_VP]),
+    "cb_trainer_profile_begin": (C.c_int, [_VP]),
+    "cb_trainer_profile_end_sync": (C.c_int, [_VP, C.POINTER(C.c_float), C.POINTER(C.c_char_p), _I, C.POINTER(C.c_int)]),
     "cb_trainer_enable_timing": (C.c_int, [_VP, _I]),
     "cb_trainer_last_hist_timing_sync": (C.c_int, [_VP, C.POINTER(C.c_float), C.POINTER(C.c_float),
                                                     C.POINTER(_I64), C.POINTER(C.c_int)]),

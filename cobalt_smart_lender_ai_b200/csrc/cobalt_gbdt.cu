@@ -464,6 +464,11 @@ struct cb_trainer_s {
   int64_t launches;
   bool timing;
   cudaEvent_t ev[3];
+  // per-launch timeline of one eager round (cb_trainer_profile_*): an event after every launch
+  bool profiling;
+  int n_marks;
+  cudaEvent_t marks[96];
+  const char* mark_names[96];
   // conflict-free histogram path
   bool cf;
   int cf_R, cf_smem;
@@ -570,7 +575,7 @@ int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, v
   t->smem = std::min(budget, t->S) * 8;
   t->grid = std::min(di.sm_count, kMaxGrid);
   t->n_part_tiles = ceil_div(cfg->n_rows, kPartTile);
-  t->cur = 0; t->identity = true; t->tree_index = 0; t->fmask = nullptr; t->launches = 0; t->timing = false;
+  t->cur = 0; t->identity = true; t->tree_index = 0; t->fmask = nullptr; t->launches = 0; t->timing = false; t->profiling = false; t->n_marks = 0;
   plan_tiles_kernel<<<1, 1>>>(buf->bin_ptr, cfg->n_features, budget, t->plan);
   set_tree_index_kernel<<<1, 1>>>(t->st, 0);
   cudaError_t e = cudaDeviceSynchronize();
@@ -619,6 +624,32 @@ void cb_trainer_destroy(cb_trainer* tr) {
   delete tr;
 }
 
+/* profile one eager round: begin -> run a round with the per-step calls -> end returns names and ms */
+int cb_trainer_profile_begin(cb_trainer* t) {
+  if (!t) return fail(CB_ERR_INVALID, "trainer: null handle");
+  if (!t->profiling) {
+    for (int i = 0; i < 96; ++i) CB_CUDA(cudaEventCreate(&t->marks[i]));
+    t->profiling = true;
+  }
+  t->n_marks = 0;
+  return CB_OK;
+}
+
+int cb_trainer_profile_end_sync(cb_trainer* t, float* ms, const char** names, int cap, int* n) {
+  if (!t || !t->profiling || !ms || !names || !n) return fail(CB_ERR_INVALID, "trainer: profiling is not active");
+  if (t->n_marks == 0) { *n = 0; return CB_OK; }
+  CB_CUDA(cudaEventSynchronize(t->marks[t->n_marks - 1]));
+  int k = 0;
+  for (int i = 1; i < t->n_marks && k < cap; ++i, ++k) {
+    CB_CUDA(cudaEventElapsedTime(&ms[k], t->marks[i - 1], t->marks[i]));
+    names[k] = t->mark_names[i];
+  }
+  *n = k;
+  for (int i = 0; i < 96; ++i) cudaEventDestroy(t->marks[i]);
+  t->profiling = false;
+  return CB_OK;
+}
+
 int cb_trainer_enable_timing(cb_trainer* t, int on) {
   if (!t) return fail(CB_ERR_INVALID, "trainer: null handle");
   if (on && !t->timing) {
@@ -644,6 +675,12 @@ int cb_trainer_last_hist_timing_sync(cb_trainer* t, float* ms_accum, float* ms_r
   return CB_OK;
 }
 
+static inline void mark(cb_trainer_s* t, cudaStream_t s, const char* name) {
+  if (!t->profiling || t->n_marks >= 96) return;
+  cudaEventRecord(t->marks[t->n_marks], s);
+  t->mark_names[t->n_marks++] = name;
+}
+
 static TreeOut tree_out(cb_trainer_s* t) {
   const size_t o = 0;   // row 0: kernels add the device-side tree index
   TreeOut to;
@@ -664,14 +701,17 @@ int cb_trainer_round_begin(cb_trainer* t, int tree_index, const uint8_t* feature
     set_tree_index_kernel<<<1, 1, 0, s>>>(t->st, tree_index);
     t->launches += 1;
   }
+  mark(t, s, "start");
   CB_CUDA(cudaMemsetAsync(t->st->root_tot, 0, 2 * sizeof(long long), s));
   int g = (int)std::min<int64_t>(ceil_div(n, 256), (int64_t)t->di.sm_count * 8);
   grad_kernel<<<g, 256, 0, s>>>(t->buf.margin, t->buf.y, t->buf.weight, n, t->cfg.scale_pos_weight,
                                 ldexpf(1.0f, t->cfg.tree.sg), ldexpf(1.0f, t->cfg.tree.sh), t->cfg.keep_thresh,
                                 t->cfg.seed, 0u, t->cfg.row_offset, t->gpair,
                                 reinterpret_cast<unsigned long long*>(t->st->root_tot), &t->st->tree_index);
+  mark(t, s, "grad");
   round_init_kernel<<<ceil_div(t->max_nodes, 256), 256, 0, s>>>(t->st, t->na, tree_out(t), t->max_nodes, (int)n,
                                                                 t->plan, t->grid);
+  mark(t, s, "round_init");
   CB_LAUNCH_CHECK();
   t->launches += 2;
   return CB_OK;
@@ -697,8 +737,10 @@ int cb_trainer_level_hist(cb_trainer* t, int level, void* stream) {
           t->buf.bins, bv.blocked ? t->cfg.n_rows : 0, bv.blocked ? bv.last_w : (int)t->cfg.ldb, t->gpair,
           t->rows[t->cur], t->plan, t->cf_lay, t->cf_fold_src, t->cf_fold_dst, t->partials);
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[1], s));
+    mark(t, s, "hist_accum");
     hist_reduce_cf_kernel<<<dim3(gx, nb, nz), 256, 0, s>>>(t->partials, t->plan, t->cf_R, t->S, t->cf_slot_of,
                                                           t->level_buf);
+    mark(t, s, "hist_reduce");
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[2], s));
   } else {
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
@@ -739,6 +781,7 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
       t->level_buf, t->pool, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S, t->st, level, t->na, t->cfg.tree, t->fmask,
       t->feat_best, level == 0 ? t->level_buf + t->S2 : nullptr, t->st, t->group_cnt, n_groups);
   t->launches += 1;
+  mark(t, s, "scan");
   LevelCtx lc;
   lc.st = t->st; lc.level = level; lc.max_depth = D; lc.f = t->cfg.n_features; lc.feat_best = t->feat_best;
   lc.p = t->cfg.tree; lc.na = t->na; lc.feat_pos = t->feat_pos;
@@ -750,16 +793,19 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
     part_level_flags_kernel<<<t->n_part_tiles + 1, 256, 0, s>>>(view, t->buf.bins_cm, rin, ident, n, t->n_part_tiles, lc, t->st,
                                                                 t->buf.cuts, t->buf.min_vals, tree_out(t), t->segs,
                                                                 t->flag_bits, t->tile_cnt, t->group_cnt);
+    mark(t, s, "flags+finish");
     part_level_scatter_kernel<<<t->n_part_tiles + 1, 256, 0, s>>>(rin, ident, n, t->n_part_tiles, t->segs, t->flag_bits,
                                                                   t->tile_cnt, t->group_cnt, rout, t->buf.margin, t->st,
                                                                   level, D, t->na, t->plan, t->grid,
                                                                   t->cfg.world_size > 1 ? 1 : 0);
+    mark(t, s, "scatter+plan");
     t->cur ^= 1; t->identity = false;
     t->launches += 2;
   } else {
     const int nblk = ceil_div(n, 256);
     final_apply_kernel<<<nblk + 1, 256, 0, s>>>(view, t->buf.bins_cm, rin, ident, n, nblk, lc, t->st, t->buf.cuts,
                                                 t->buf.min_vals, tree_out(t), t->segs, t->buf.margin);
+    mark(t, s, "final_apply");
     t->launches += 1;
   }
   CB_LAUNCH_CHECK();

@@ -164,6 +164,16 @@ class GpuTrainer:
         self._graphs[key] = graph
         return graph
 
+    def profile_round(self, feature_masks: torch.Tensor | None = None):
+        """Runs ONE eager round with a CUDA event after every launch; returns [(step name, ms), ...]."""
+        check(self.lib.cb_trainer_profile_begin(self.handle))
+        self.boost_one(feature_masks)
+        ms = (C.c_float * 96)()
+        names = (C.c_char_p * 96)()
+        n = C.c_int(0)
+        check(self.lib.cb_trainer_profile_end_sync(self.handle, ms, names, 96, C.byref(n)))
+        return [(names[i].decode(), float(ms[i])) for i in range(n.value)]
+
     def launch_count_raw(self) -> int:
         return int(self.lib.cb_trainer_launch_count(self.handle))
 

@@ -226,6 +226,10 @@ int cb_trainer_node_hist(cb_trainer* tr, int node_id, const int64_t** ptr);
  * last_hist_timing_sync blocks until the last level_hist finished and also returns the rows it scanned. */
 int cb_trainer_enable_timing(cb_trainer* tr, int on);
 int cb_trainer_last_hist_timing_sync(cb_trainer* tr, float* ms_accum, float* ms_reduce, int64_t* rows, int* n_build);
+/* per-launch timeline of one round (warm caches, back to back): profile_begin, then one round through the
+ * calls above, then profile_end_sync returns the elapsed ms between consecutive launches and their names */
+int cb_trainer_profile_begin(cb_trainer* tr);
+int cb_trainer_profile_end_sync(cb_trainer* tr, float* ms, const char** names, int capacity, int* n);
 /* kernels launched by this trainer so far (bench.py's gpu_launches) */
 int64_t cb_trainer_launch_count(cb_trainer* tr);
 

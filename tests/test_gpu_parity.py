@@ -365,6 +365,25 @@ def test_train_150_features_two_column_blocks(ops):
     assert np.array_equal(_final_rows(ref, tr, ref["bins"]), ref["forest"]["row_order"])
 
 
+@pytest.mark.parametrize("n,f,depth", [(1, 1, 2), (2, 3, 3), (33, 5, 4), (257, 33, 5), (1000, 129, 9), (5000, 2, 6)])
+def test_train_tiny_and_odd_shapes(ops, n, f, depth):
+    """Ragged sizes: single rows, one feature, more than one column block with few rows, maximum depth."""
+    rng = np.random.default_rng(n * 131 + f)
+    X = rng.normal(size=(n, f)).astype(np.float32)
+    X[:, ::2] = np.round(X[:, ::2] * 2)                       # low-cardinality columns
+    X[rng.random(X.shape) < 0.1] = np.nan
+    y = (rng.random(n) < 0.4).astype(np.uint8)
+    if n > 1:
+        y[0], y[1] = 0, 1
+    ref = O.fit_reference(X, y, n_estimators=5, max_depth=depth, scale_pos_weight=1.5, min_child_weight=0.0, base_score=0.5)
+    tr = _train_gpu(ops, ref, X, y, 5, 1.5)
+    _assert_forest_equal(tr.forest_numpy(), ref["flat"])
+    assert np.array_equal(tr.margin.cpu().numpy().view(np.uint32), ref["margin"].view(np.uint32))
+    from cobalt_smart_lender_ai_b200.booster import Booster
+    m = Booster(tr.forest_numpy(), f, None, 0.5).predict_device(_dev(X), output_margin=True).cpu().numpy()
+    assert np.array_equal(m.view(np.uint32), ref["margin"].view(np.uint32))
+
+
 def test_train_colsample_and_weights(ops, data):
     from cobalt_smart_lender_ai_b200.sklearn import colsample_masks
     X, y, _ = data
