@@ -790,11 +790,12 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   const int ident = t->identity ? 1 : 0;
   if (level + 1 < D) {
     uint32_t* rout = t->rows[t->cur ^ 1];
-    part_level_flags_kernel<<<t->n_part_tiles + 1, 256, 0, s>>>(view, t->buf.bins_cm, rin, ident, n, t->n_part_tiles, lc, t->st,
+    const int pgrid = std::min(t->n_part_tiles, t->di.sm_count * 5) + 1;     // 5 CTAs per SM resident: whole waves
+    part_level_flags_kernel<<<pgrid, 256, 0, s>>>(view, t->buf.bins_cm, rin, ident, n, t->n_part_tiles, lc, t->st,
                                                                 t->buf.cuts, t->buf.min_vals, tree_out(t), t->segs,
                                                                 t->flag_bits, t->tile_cnt, t->group_cnt);
     mark(t, s, "flags+finish");
-    part_level_scatter_kernel<<<t->n_part_tiles + 1, 256, 0, s>>>(rin, ident, n, t->n_part_tiles, t->segs, t->flag_bits,
+    part_level_scatter_kernel<<<pgrid, 256, 0, s>>>(rin, ident, n, t->n_part_tiles, t->segs, t->flag_bits,
                                                                   t->tile_cnt, t->group_cnt, rout, t->buf.margin, t->st,
                                                                   level, D, t->na, t->plan, t->grid,
                                                                   t->cfg.world_size > 1 ? 1 : 0);
@@ -802,7 +803,7 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
     t->cur ^= 1; t->identity = false;
     t->launches += 2;
   } else {
-    const int nblk = ceil_div(n, 256);
+    const int nblk = ceil_div(n, 1024);
     final_apply_kernel<<<nblk + 1, 256, 0, s>>>(view, t->buf.bins_cm, rin, ident, n, nblk, lc, t->st, t->buf.cuts,
                                                 t->buf.min_vals, tree_out(t), t->segs, t->buf.margin);
     mark(t, s, "final_apply");

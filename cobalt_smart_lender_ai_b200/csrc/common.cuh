@@ -99,6 +99,9 @@ __device__ __forceinline__ uint32_t spec_hash(uint32_t seed, uint32_t a, uint64_
   return h;
 }
 
+// 2^-s as a double, exactly (s in [-1000, 1000]): replaces a library ldexp call in per-thread prologues
+__device__ __forceinline__ double pow2neg(int s) { return __longlong_as_double((long long)(1023 - s) << 52); }
+
 // ---- R6 gain / weight in f64, one rounding per operation
 __device__ __forceinline__ double thr_l1(double g, double a) {
   if (g > a) return __dsub_rn(g, a);
@@ -117,6 +120,6 @@ __device__ __forceinline__ double calc_weight(double G, double H, const cb_tree_
 }
 
 constexpr int kChunkRows = 16352;  // rows per int32 partial histogram: 16352 * 2^17 < 2^31
-constexpr int kPartTile = 2048;    // positions per partition tile
+constexpr int kPartTile = 1024;    // positions per partition tile
 
 }  // namespace cb

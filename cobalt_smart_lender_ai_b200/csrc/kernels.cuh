@@ -323,7 +323,7 @@ __device__ __forceinline__ float split_chg(int64_t gl, int64_t hl, int64_t gr, i
 __device__ __forceinline__ FeatBest scan_feature(const int64_t* __restrict__ hist, int nb, int64_t Gt, int64_t Ht,
                                                  const cb_tree_params& p) {
   const int lane = threadIdx.x & 31;
-  const double ig = ldexp(1.0, -p.sg), ih = ldexp(1.0, -p.sh);
+  const double ig = pow2neg(p.sg), ih = pow2neg(p.sh);
   const float root_gain = __double2float_rn(calc_gain(__dmul_rn((double)Gt, ig), __dmul_rn((double)Ht, ih), p));
   int64_t g[8], h[8];
   int64_t sg = 0, sh = 0;

@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
     Gf += sg[w]; Hf += sh[w];
   }
   const long long exg = wg + ig - tg, exh = wh + ih - th;     // sum of all bins before 2 * tid
-  const double dg = ldexp(1.0, -p.sg), dh = ldexp(1.0, -p.sh);
+  const double dg = pow2neg(p.sg), dh = pow2neg(p.sh);
   const float root_gain = __double2float_rn(calc_gain(__dmul_rn((double)Gt, dg), __dmul_rn((double)Ht, dh), p));
   // forward (missing -> right): candidate b has left = prefix_incl(b); scan order ascending
   float fc = 0.0f; int fbin = -1;
@@ -245,7 +245,7 @@ struct LevelCtx {
 // kind / split / leaf values of every node of the level, recomputed by whoever needs them
 __device__ void build_node_table(NodeTable& nt, const LevelCtx& c, bool want_leaves) {
   const int first = c.st->lvl_first[c.level], cnt = c.st->lvl_count[c.level];
-  const double dg = ldexp(1.0, -c.p.sg), dh = ldexp(1.0, -c.p.sh);
+  const double dg = pow2neg(c.p.sg), dh = pow2neg(c.p.sh);
   for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
     const int nid = first + i;
     const unsigned long long key = __ldg(&c.st->best_key[i]);
@@ -290,7 +290,7 @@ __device__ void build_node_table(NodeTable& nt, const LevelCtx& c, bool want_lea
 __device__ void finish_level(TreeState* st, const LevelCtx& c, const float* __restrict__ cuts,
                              const float* __restrict__ min_vals, TreeOut to, LevelSegs* segs, int* s_child) {
   const int first = st->lvl_first[c.level], cnt = st->lvl_count[c.level];
-  const double dg = ldexp(1.0, -c.p.sg), dh = ldexp(1.0, -c.p.sh);
+  const double dg = pow2neg(c.p.sg), dh = pow2neg(c.p.sh);
   for (int i = threadIdx.x; i < cnt; i += blockDim.x) {      // validity again (cheap), 1 = splits
     const unsigned long long key = __ldcg(&st->best_key[i]);
     int v = 0;
@@ -404,12 +404,12 @@ __global__ void __launch_bounds__(256) part_level_flags_kernel(BinsView view, co
     finish_level(stw, c, cuts, min_vals, tree_slice(to, stw, (1 << (c.max_depth + 1)) - 1), segs, nt.begin);
     return;
   }
-  const int tile = (int)blockIdx.x - 1;
   build_node_table(nt, c, false);
   const int n = c.st->lvl_count[c.level];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int tile0 = tile * kPartTile;
   constexpr int IT = kPartTile / 256;
+  for (int tile = (int)blockIdx.x - 1; tile < n_tiles; tile += (int)gridDim.x - 1) {   // whole waves: no tail
+  const int tile0 = tile * kPartTile;
   uint32_t row[IT];
   int seg[IT];
 #pragma unroll
@@ -451,6 +451,8 @@ __global__ void __launch_bounds__(256) part_level_flags_kernel(BinsView view, co
     for (int k = 0; k < 8; ++k) t += wsum[k];
     tile_cnt[tile] = t;
     if (t) atomicAdd(group_cnt + tile / kTileGroup, t);
+  }
+  __syncthreads();
   }
 }
 
@@ -550,11 +552,11 @@ __global__ void __launch_bounds__(256) part_level_scatter_kernel(const uint32_t*
     plan_next_level(st, level, max_depth, na, segs, group_cnt, tile_cnt, flag_bits, n_rows, plan, grid, by_hessian, psm);
     return;
   }
-  const int tile = (int)blockIdx.x - 1;
   const int n = segs->n;
   for (int i = threadIdx.x; i < n; i += blockDim.x) { sc.begin[i] = segs->begin[i]; sc.count[i] = segs->count[i]; }
   __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int tile = (int)blockIdx.x - 1; tile < n_tiles; tile += (int)gridDim.x - 1) {   // whole waves: no tail
   const int tile0 = tile * kPartTile;
   const int tile_end = min(n_rows, tile0 + kPartTile);
   // segments that overlap this tile: [s_lo, s_hi]
@@ -575,35 +577,49 @@ __global__ void __launch_bounds__(256) part_level_scatter_kernel(const uint32_t*
     if (lane == 0) { s_Lb[i] = Lb; s_nl[i] = Le - Lb; }
   }
   __syncthreads();
-  const int w0 = tile0 >> 5, wpw = kPartTile / 8 / 32;
+  constexpr int wpw = kPartTile / 8 / 32;
+  const int w0 = tile0 >> 5;
   int before = 0;
   for (int k = lane; k < wid * wpw; k += 32)
     if ((w0 + k) * 32 < n_rows) before += __popc(flag_bits[w0 + k]);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) before += __shfl_xor_sync(0xffffffffu, before, o);
   int run = s_prefix + before;
-  for (int it = 0; it < wpw; ++it) {
+  uint32_t bal[wpw], row[wpw];
+  int seg[wpw];
+#pragma unroll
+  for (int it = 0; it < wpw; ++it) {                 // all loads of the warp's 256 positions first
     const int pos0 = tile0 + wid * (kPartTile / 8) + it * 32;
     const int pos = pos0 + lane;
-    if (pos0 >= n_rows) break;
-    const uint32_t bal = flag_bits[pos >> 5];
-    const int i = find_seg_warp(sc.begin, sc.count, n, pos0, lane);
-    if (pos < n_rows) {
-      const uint32_t row = identity ? (uint32_t)pos : __ldg(rows_in + pos);
+    bal[it] = 0; row[it] = 0; seg[it] = -2;
+    if (pos0 < n_rows) {
+      bal[it] = flag_bits[pos0 >> 5];
+      seg[it] = find_seg_warp(sc.begin, sc.count, n, pos0, lane);
+      if (pos < n_rows) row[it] = identity ? (uint32_t)pos : __ldg(rows_in + pos);
+      else seg[it] = -2;
+    }
+  }
+#pragma unroll
+  for (int it = 0; it < wpw; ++it) {
+    const int pos = tile0 + wid * (kPartTile / 8) + it * 32 + lane;
+    if (seg[it] != -2) {
+      const int i = seg[it];
       int dest = pos;
       if (i >= 0) {
         const int kind = segs->kind[i];
         if (kind == 1) {
-          const int lb = run + __popc(bal & ((1u << lane) - 1u)) - s_Lb[i];   // lefts before, inside the node
+          const int lb = run + __popc(bal[it] & ((1u << lane) - 1u)) - s_Lb[i];   // lefts before, inside the node
           const int bg = sc.begin[i];
-          dest = ((bal >> lane) & 1u) ? bg + lb : bg + s_nl[i] + (pos - bg - lb);
+          dest = ((bal[it] >> lane) & 1u) ? bg + lb : bg + s_nl[i] + (pos - bg - lb);
         } else if (kind == 0) {
-          margin[row] = __fadd_rn(margin[row], segs->leafL[i]);
+          margin[row[it]] = __fadd_rn(margin[row[it]], segs->leafL[i]);
         }
       }
-      rows_out[dest] = row;
+      rows_out[dest] = row[it];
     }
-    run += __popc(bal);
+    run += __popc(bal[it]);
+  }
+  __syncthreads();
   }
 }
 
@@ -623,18 +639,41 @@ __global__ void __launch_bounds__(256) final_apply_kernel(BinsView view, const u
   build_node_table(nt, c, true);
   const int n = c.st->lvl_count[c.level];
   const int lane = threadIdx.x & 31;
-  const int pos = ((int)blockIdx.x - 1) * blockDim.x + threadIdx.x;
-  const int i = find_seg_warp(nt.begin, nt.count, n, pos - lane, lane);
-  if (pos >= n_rows || i < 0) return;
-  const uint32_t row = identity ? (uint32_t)pos : __ldg(rows_in + pos);
-  const int m = nt.meta[i];
-  float leaf = nt.leafL[i];
-  if ((m >> 24) == 2) {
-    const int cd = code_at(view, bins_cm, row, m & 0xFFFF);
-    const bool left = cd == CB_MISSING_BIN ? ((m >> 16) & 1) != 0 : cd <= nt.bin[i];
-    if (!left) leaf = nt.leafR[i];
+  constexpr int IT = 4;                                // positions per thread, loads batched
+  const int base = ((int)blockIdx.x - 1) * (blockDim.x * IT) + (threadIdx.x & ~31) * IT;
+  uint32_t row[IT];
+  int seg[IT], code[IT];
+#pragma unroll
+  for (int it = 0; it < IT; ++it) {
+    const int pos0 = base + it * 32, pos = pos0 + lane;
+    seg[it] = -1; row[it] = 0;
+    if (pos0 < n_rows) {
+      const int i = find_seg_warp(nt.begin, nt.count, n, pos0, lane);
+      if (pos < n_rows && i >= 0) {
+        seg[it] = i;
+        row[it] = identity ? (uint32_t)pos : __ldg(rows_in + pos);
+      }
+    }
   }
-  margin[row] = __fadd_rn(margin[row], leaf);
+#pragma unroll
+  for (int it = 0; it < IT; ++it) {
+    code[it] = 0;
+    if (seg[it] >= 0 && (nt.meta[seg[it]] >> 24) == 2) code[it] = code_at(view, bins_cm, row[it], nt.meta[seg[it]] & 0xFFFF);
+  }
+  float mg[IT];
+#pragma unroll
+  for (int it = 0; it < IT; ++it) mg[it] = seg[it] >= 0 ? margin[row[it]] : 0.0f;
+#pragma unroll
+  for (int it = 0; it < IT; ++it) {
+    if (seg[it] < 0) continue;
+    const int m = nt.meta[seg[it]];
+    float leaf = nt.leafL[seg[it]];
+    if ((m >> 24) == 2) {
+      const bool left = code[it] == CB_MISSING_BIN ? ((m >> 16) & 1) != 0 : code[it] <= nt.bin[seg[it]];
+      if (!left) leaf = nt.leafR[seg[it]];
+    }
+    margin[row[it]] = __fadd_rn(mg[it], leaf);
+  }
 }
 
 __global__ void round_end_kernel(TreeState* st, int32_t* n_nodes_all) {
