@@ -167,6 +167,7 @@ def run_ours(args):
     lib.cb_trainer_enable_timing(tr.handle, 1)
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     acc_ms = red_ms = 0.0
+    per_level = {}
     alg_bytes = 0
     n_launch = 0
     for _ in range(3):
@@ -179,6 +180,7 @@ def run_ours(args):
                 torch.distributed.all_reduce(tr._level_view(level), group=tr.group)
             _lib.check(lib.cb_trainer_level_split(tr.handle, level, st))
             acc_ms += a.value; red_ms += r_.value; n_launch += 1
+            per_level.setdefault(level, []).append((int(rows.value), int(nb.value), round(a.value * 1e3, 1)))
             # R*(F + 8 + 4) + nodes_built*F*B*16 ; the row-index term is 0 at the root
             alg_bytes += rows.value * (N_FEAT + 8 + (0 if level == 0 else 4)) + nb.value * N_FEAT * 256 * 16
         _lib.check(lib.cb_trainer_round_end(tr.handle, st))
@@ -196,7 +198,8 @@ def run_ours(args):
                 "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                 "avg_launch_ms": round(acc_ms / n_launch, 4), "launches_timed": n_launch,
                 "alg_bytes_per_launch": int(alg_bytes / n_launch), "hist_reduce_ms_per_launch": round(red_ms / n_launch, 4),
-                "hist_share_of_round": round((acc_ms + red_ms) / 3 / (ms / args.steps), 3)}
+                "hist_share_of_round": round((acc_ms + red_ms) / 3 / (ms / args.steps), 3),
+                "per_level_rows_nodes_us": {str(k): v[-1] for k, v in per_level.items()}}
     auc = None
     try:
         from sklearn.metrics import roc_auc_score
