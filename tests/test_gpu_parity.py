@@ -538,3 +538,34 @@ def test_scoring_service_on_gpu(ops, fixture_forest, tmp_path):
     assert r.status_code == 200 and abs(r.json()["prob_default"] - want[0]) <= 1e-5
     r = client.post("/feature_importance_bulk", json={"data": [row]})
     assert r.json()["top_features"][0]["feature"] in names
+
+
+def test_reference_training_job_flow(ops):
+    """The reference's training script, steps 2-7 (leakage drop, split, RFE to 20 features,
+    RandomizedSearchCV, test metrics, joblib dump/load), on synthetic loans -- with this package's
+    XGBClassifier as the only change (model_train_test mirror)."""
+    import io
+
+    import joblib
+    import pandas as pd
+
+    from cobalt_smart_lender_ai_b200.model_train_test.model_tree_train_test import train_pipeline
+    from cobalt_smart_lender_ai_b200.synth import make_lending
+    X, y, names = make_lending(12000, 26, seed=21)
+    df = pd.DataFrame(X.numpy(), columns=names)
+    for c in names[-4:]:
+        df[c] = df[c].astype(bool)
+    df["loan_default"] = y.numpy().astype(int)
+    df["total_pymnt"] = 1.0                                       # a leakage column that must be dropped
+    out = train_pipeline(df, n_features_to_select=20, n_iter=3, cv=3,
+                         param_distributions={"n_estimators": [20, 30], "max_depth": [3, 5], "learning_rate": [0.1],
+                                              "subsample": [0.8, 1.0], "colsample_bytree": [0.5, 1.0], "gamma": [0, 1]})
+    assert len(out["selected_features"]) == 20 and "total_pymnt" not in out["selected_features"]
+    assert 0.6 < out["metrics"]["auc"] <= 1.0 and 0.6 < out["cv_best_score"] <= 1.0
+    assert abs(sum(out["feature_importances"].values()) - 1.0) < 1e-4
+    buf = io.BytesIO()
+    joblib.dump(out["model"], buf)
+    buf.seek(0)
+    again = joblib.load(buf)
+    Xs = df[out["selected_features"]].iloc[:50]
+    assert np.array_equal(again.predict_proba(Xs), out["model"].predict_proba(Xs))
