@@ -11,18 +11,27 @@ from cobalt_smart_lender_ai_b200 import ops  # noqa: E402
 from cobalt_smart_lender_ai_b200.synth import make_lending  # noqa: E402
 from cobalt_smart_lender_ai_b200.trainer import GpuTrainer  # noqa: E402
 
+from cobalt_smart_lender_ai_b200 import parallel  # noqa: E402
+
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 2_200_000
 f = 150
-X, y, _ = make_lending(n, f, device="cuda")
-cuts, n_cuts, min_vals = ops.sketch_cuts(X, 256)
+world = int(os.environ.get("WORLD_SIZE", "1"))
+rank = int(os.environ.get("RANK", "0"))
+if world > 1:
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+r0, r1 = parallel.shard_rows(n, rank, world)
+X, y, _ = make_lending(r1 - r0, f, row_offset=r0, device="cuda")
+cuts, n_cuts, min_vals = parallel.sketch_cuts_global(X, 256)
 pos_np, cf = ops.plan_layout(n_cuts, f)
 pos = torch.from_numpy(pos_np).cuda()
 bins = ops.bin_pack(X, cuts, n_cuts, pos_feature=pos, blocked=cf)
 cm = ops.bin_transpose(bins, blocked=cf)
-spw = float(((y == 0).sum() / (y == 1).sum()).item())
+spw = 6.75
 sg, sh = ops.quant_shifts(spw)
 tr = GpuTrainer(bins, y, None, f, ops.bin_ptr_of(n_cuts), cuts, min_vals, max_depth=6, eta=0.3, scale_pos_weight=spw,
-                sg=sg, sh=sh, max_trees=40, group=False, pos_feature=pos, blocked=cf, bins_cm=cm)
+                sg=sg, sh=sh, max_trees=40, group=None if world > 1 else False, pos_feature=pos, blocked=cf, bins_cm=cm,
+                row_offset=r0)
 tr.boost(10, use_graph=False)
 agg = collections.OrderedDict()
 rounds = 5
@@ -31,6 +40,8 @@ for _ in range(rounds):
     for k, v in tl:
         agg.setdefault(k, []).append(v)
 tot = sum(sum(v) for v in agg.values()) / rounds
+if rank != 0:
+    sys.exit(0)
 for k, v in agg.items():
     per = len(v) // rounds
     print(f"{k:14s} x{per}  {1e3 * sum(v) / rounds:8.1f} us/round  {100 * sum(v) / rounds / tot:5.1f}%   per launch: "
