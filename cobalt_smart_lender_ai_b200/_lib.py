@@ -109,6 +109,13 @@ _SIGS = {
     "cb_trainer_level_split": (C.c_int, [_VP, _I, _VP]),
     "cb_trainer_round_end": (C.c_int, [_VP, _VP]),
     "cb_trainer_level_buffer": (C.c_int, [_VP, _I, C.POINTER(_VP), C.POINTER(_I64)]),
+    "cb_sym_alloc": (C.c_int, [_SZ, C.POINTER(_VP), _VP]),
+    "cb_sym_open": (C.c_int, [_VP, C.POINTER(_VP)]),
+    "cb_sym_close": (C.c_int, [_VP]),
+    "cb_sym_free": (C.c_int, [_VP]),
+    "cb_trainer_sym_bytes": (C.c_int, [C.POINTER(TrainConfig), C.POINTER(_SZ)]),
+    "cb_trainer_set_peers": (C.c_int, [_VP, _I, _I, C.POINTER(_VP)]),
+    "cb_trainer_peer_status": (C.c_int, [_VP, C.POINTER(C.c_int)]),
     "cb_trainer_row_order": (C.c_int, [_VP, C.POINTER(_VP)]),
     "cb_trainer_node_hist": (C.c_int, [_VP, _I, C.POINTER(_VP)]),
     "cb_trainer_launch_count": (C.c_int64, [_VP]),

@@ -478,6 +478,10 @@ struct cb_trainer_s {
   int32_t* cf_fold_dst;
   int32_t* feat_pos;      // [f] byte position of a feature inside a binned row
   int part_words;         // int32 words per partial histogram
+  // peer mode (row-sharded training over NVLink peer memory)
+  PeerCtx pc;
+  SymHeader** d_peers;
+  int64_t** d_peer_lb;
 };
 
 static int trainer_layout(const cb_train_config* cfg, const DeviceInfo& di, void* ws, cb_trainer_s* t, size_t* bytes) {
@@ -514,6 +518,8 @@ static int trainer_layout(const cb_train_config* cfg, const DeviceInfo& di, void
   int32_t* cf_fold_src = b.take<int32_t>((size_t)cf_words);
   int32_t* cf_fold_dst = b.take<int32_t>((size_t)cf_words);
   int32_t* feat_pos = b.take<int32_t>((size_t)cfg->n_features);
+  SymHeader** d_peers = b.take<SymHeader*>(kMaxRanks);
+  int64_t** d_peer_lb = b.take<int64_t*>(kMaxRanks);
   if (bytes) *bytes = b.used();
   if (t) {
     t->max_nodes = max_nodes; t->S = S; t->S2 = 2 * S; t->pool_slots = pool_slots; t->lb_slots = lb_slots;
@@ -523,6 +529,7 @@ static int trainer_layout(const cb_train_config* cfg, const DeviceInfo& di, void
     t->partials = partials; t->feat_best = feat_best;
     t->cf_lay = cf_lay; t->cf_slot_of = cf_slot_of; t->cf_fold_src = cf_fold_src; t->cf_fold_dst = cf_fold_dst;
     t->feat_pos = feat_pos; t->part_words = part_words;
+    t->d_peers = d_peers; t->d_peer_lb = d_peer_lb;
   }
   return CB_OK;
 }
@@ -576,8 +583,9 @@ int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, v
   t->grid = std::min(di.sm_count, kMaxGrid);
   t->n_part_tiles = ceil_div(cfg->n_rows, kPartTile);
   t->cur = 0; t->identity = true; t->tree_index = 0; t->fmask = nullptr; t->launches = 0; t->timing = false; t->profiling = false; t->n_marks = 0;
+  memset(&t->pc, 0, sizeof t->pc); t->pc.world = 1;
   plan_tiles_kernel<<<1, 1>>>(buf->bin_ptr, cfg->n_features, budget, t->plan);
-  set_tree_index_kernel<<<1, 1>>>(t->st, 0);
+  init_state_kernel<<<1, 1>>>(t->st);
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { delete t; return fail(CB_ERR_CUDA, "cb_trainer_create: %s", cudaGetErrorString(e)); }
   // column placement -> conflict-free shared-memory tables (host side, one-off)
@@ -757,6 +765,11 @@ int cb_trainer_level_hist(cb_trainer* t, int level, void* stream) {
     root_totals_kernel<<<1, 1, 0, s>>>(t->st, t->level_buf + t->S2);
     t->launches += 1;
   }
+  if (t->pc.world > 1) {                  // peers may now read this rank's level buffer
+    peer_signal_kernel<<<1, 32, 0, s>>>(t->pc, t->st, level, 0);
+    t->launches += 1;
+    mark(t, s, "signal");
+  }
   CB_LAUNCH_CHECK();
   return CB_OK;
 }
@@ -777,14 +790,22 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   const int ln = 1 << level;
   const int n = (int)t->cfg.n_rows;
   const int n_groups = ceil_div(t->n_part_tiles, kTileGroup);
-  scan_level_fused_kernel<<<dim3(t->cfg.n_features, ln), 128, 0, s>>>(
-      t->level_buf, t->pool, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S, t->st, level, t->na, t->cfg.tree, t->fmask,
-      t->feat_best, level == 0 ? t->level_buf + t->S2 : nullptr, t->st, t->group_cnt, n_groups);
-  t->launches += 1;
+  const int fx = t->pc.world > 1 ? t->pc.f1 - t->pc.f0 : t->cfg.n_features;   // peer mode: this rank's feature slice
+  if (fx > 0) {
+    scan_level_fused_kernel<<<dim3(fx, ln), 128, 0, s>>>(
+        t->level_buf, t->pool, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S, t->st, level, t->na, t->cfg.tree, t->fmask,
+        t->feat_best, level == 0 ? t->level_buf + t->S2 : nullptr, t->st, t->group_cnt, n_groups, t->pc);
+    t->launches += 1;
+  }
   mark(t, s, "scan");
+  if (t->pc.world > 1) {
+    peer_publish_kernel<<<1, 256, 0, s>>>(t->pc, t->st, level, t->feat_best, t->cfg.n_features);
+    t->launches += 1;
+    mark(t, s, "publish");
+  }
   LevelCtx lc;
   lc.st = t->st; lc.level = level; lc.max_depth = D; lc.f = t->cfg.n_features; lc.feat_best = t->feat_best;
-  lc.p = t->cfg.tree; lc.na = t->na; lc.feat_pos = t->feat_pos;
+  lc.p = t->cfg.tree; lc.na = t->na; lc.feat_pos = t->feat_pos; lc.pc = t->pc;
   const BinsView view = make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked);
   const uint32_t* rin = t->rows[t->cur];
   const int ident = t->identity ? 1 : 0;
@@ -829,6 +850,81 @@ int cb_trainer_boost_round(cb_trainer* t, int tree_index, const uint8_t* feature
     if ((rc = cb_trainer_level_split(t, level, stream))) return rc;
   }
   return cb_trainer_round_end(t, stream);
+}
+
+// ---------------------------------------------------------------------------- peer memory (CUDA IPC)
+int cb_sym_alloc(size_t bytes, void** ptr, unsigned char* handle64) {
+  if (!ptr || !handle64 || bytes == 0) return fail(CB_ERR_INVALID, "cb_sym_alloc: bad arguments");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  void* p = nullptr;
+  CB_CUDA(cudaMalloc(&p, bytes));
+  CB_CUDA(cudaMemset(p, 0, bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) { cudaFree(p); return fail(CB_ERR_CUDA, "cb_sym_alloc: cudaIpcGetMemHandle: %s", cudaGetErrorString(e)); }
+  memcpy(handle64, &h, 64);
+  *ptr = p;
+  return CB_OK;
+}
+int cb_sym_open(const unsigned char* handle64, void** ptr) {
+  if (!ptr || !handle64) return fail(CB_ERR_INVALID, "cb_sym_open: bad arguments");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  CB_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return CB_OK;
+}
+int cb_sym_close(void* ptr) { if (ptr) CB_CUDA(cudaIpcCloseMemHandle(ptr)); return CB_OK; }
+int cb_sym_free(void* ptr) { if (ptr) CB_CUDA(cudaFree(ptr)); return CB_OK; }
+
+static size_t sym_lb_offset() { return (sizeof(SymHeader) + 255) & ~size_t(255); }
+
+int cb_trainer_sym_bytes(const cb_train_config* cfg, size_t* bytes) {
+  int rc = trainer_check_cfg(cfg);
+  if (rc) return rc;
+  if (!bytes) return fail(CB_ERR_INVALID, "cb_trainer_sym_bytes: null output");
+  const int D = cfg->tree.max_depth;
+  const int lb_slots = D >= 2 ? (1 << (D - 2)) : 1;
+  *bytes = sym_lb_offset() + sizeof(int64_t) * ((size_t)lb_slots * 2 * cfg->total_bins + 2) + 256;
+  return CB_OK;
+}
+
+int cb_trainer_set_peers(cb_trainer* t, int rank, int world, void* const* regions) {
+  if (!t || !regions || world < 2 || world > kMaxRanks || rank < 0 || rank >= world)
+    return fail(CB_ERR_INVALID, "cb_trainer_set_peers: bad arguments (2 <= world <= %d)", kMaxRanks);
+  if (world != t->cfg.world_size) return fail(CB_ERR_INVALID, "cb_trainer_set_peers: world differs from cb_train_config.world_size");
+  SymHeader* hp[kMaxRanks] = {nullptr};
+  int64_t* lp[kMaxRanks] = {nullptr};
+  for (int r = 0; r < world; ++r) {
+    if (!regions[r]) return fail(CB_ERR_INVALID, "cb_trainer_set_peers: region %d is null", r);
+    hp[r] = reinterpret_cast<SymHeader*>(regions[r]);
+    lp[r] = reinterpret_cast<int64_t*>(reinterpret_cast<char*>(regions[r]) + sym_lb_offset());
+  }
+  CB_CUDA(cudaMemcpy(t->d_peers, hp, sizeof hp, cudaMemcpyHostToDevice));
+  CB_CUDA(cudaMemcpy(t->d_peer_lb, lp, sizeof lp, cudaMemcpyHostToDevice));
+  // feature slices balanced by histogram slots
+  const int f = t->cfg.n_features;
+  std::vector<int32_t> bp((size_t)f + 1);
+  CB_CUDA(cudaMemcpy(bp.data(), t->buf.bin_ptr, sizeof(int32_t) * (f + 1), cudaMemcpyDeviceToHost));
+  int bounds[kMaxRanks + 1];
+  bounds[0] = 0;
+  int feat = 0;
+  for (int r = 1; r <= world; ++r) {
+    const long long target = (long long)bp[f] * r / world;
+    while (feat < f && bp[feat + 1] <= target) ++feat;
+    bounds[r] = r == world ? f : feat;
+  }
+  t->pc.world = world; t->pc.rank = rank; t->pc.f0 = bounds[rank]; t->pc.f1 = bounds[rank + 1];
+  t->pc.self = hp[rank]; t->pc.peers = t->d_peers; t->pc.peer_level_buf = t->d_peer_lb;
+  t->level_buf = lp[rank];
+  return CB_OK;
+}
+
+int cb_trainer_peer_status(cb_trainer* t, int* timed_out) {
+  if (!t || !timed_out) return fail(CB_ERR_INVALID, "cb_trainer_peer_status: bad arguments");
+  unsigned v = 0;
+  CB_CUDA(cudaMemcpy(&v, &t->st->peer_timeout, sizeof v, cudaMemcpyDeviceToHost));
+  *timed_out = (int)v;
+  return CB_OK;
 }
 
 int cb_trainer_row_order(cb_trainer* t, const uint32_t** ptr) {

@@ -13,6 +13,8 @@ struct TreeState {                        // device memory
   int lvl_count[kMaxDepth + 2];
   int tree_index;                         // forest row being grown; advanced by round_end (graph replay needs no host value)
   long long root_tot[2];                  // local sum of (q_g, q_h), filled by the gradient kernel
+  unsigned int round_seq;                 // rounds finished so far (peer mode: base of the flag epochs)
+  unsigned int peer_timeout;              // set when a wait on a peer flag gave up (never in a healthy run)
   unsigned long long best_key[kMaxLevelNodes];  // per level node: max over features of (chg bits << 32 | 0xFFFF - feature)
 };
 
@@ -34,6 +36,59 @@ struct TreeOut {                          // slices of the forest arrays for the
   float* split_cond; uint8_t* default_left; float* base_weight; float* loss_chg; float* sum_hess;
 };
 
+// ---------------------------------------------------------------------------------------------------
+// Row-sharded training over NVLink peer memory (no NCCL on the critical path).  Every rank owns one
+// "symmetric" region (same layout on every GPU, mapped into every peer with CUDA IPC):
+//   flags[2][kMaxRanks]   epoch counters written BY peers: [0] "my level buffer is complete",
+//                         [1] "my best candidates of this level are in your table"
+//   tab[kMaxRanks][256]   best candidate of each level node, one row per source rank (written by peers)
+//   level buffer          this rank's LOCAL histograms of the level's built nodes (+2 root totals)
+// The scan kernel of rank r handles only r's slice of the features: it adds that slice of all ranks'
+// level buffers (peer loads over NVLink) on the fly -- the collective is fused into the scan, the full
+// histogram never travels -- and publishes one candidate per node to every peer.
+// ---------------------------------------------------------------------------------------------------
+constexpr int kMaxRanks = 16;
+struct PeerBest { unsigned long long key; int split_bin; int dl; long long GL; long long HL; };
+struct SymHeader {
+  unsigned int flags[2][kMaxRanks];
+  unsigned int pad_[32];
+  PeerBest tab[kMaxRanks][kMaxLevelNodes];
+};
+struct PeerCtx {                           // by value into kernels; world <= 1 means single-GPU mode
+  int world, rank;
+  int f0, f1;                              // this rank's feature slice
+  SymHeader* self;                         // own region (peers write into it)
+  SymHeader* const* peers;                 // device array [world] of all regions (peer-mapped addresses)
+  int64_t* const* peer_level_buf;          // device array [world] of all level buffers
+};
+
+__device__ __forceinline__ unsigned peer_epoch(const TreeState* st, int level, int phase) {
+  return st->round_seq * 64u + (unsigned)level * 2u + (unsigned)phase + 1u;
+}
+// one thread: block until every peer's flag of `phase` reached `epoch` (bounded: a dead peer must not hang the GPU)
+__device__ __forceinline__ void peer_wait(const PeerCtx& pc, TreeState* st, int phase, unsigned epoch) {
+  for (int r = 0; r < pc.world; ++r) {
+    volatile unsigned* fl = &pc.self->flags[phase][r];
+    unsigned long long spins = 0;
+    while ((int)(*fl - epoch) < 0) {
+      if (++spins > (1ull << 24)) { st->peer_timeout = 1; break; }
+      __nanosleep(64);
+    }
+  }
+  __threadfence_system();
+}
+// tell every peer that `phase` of this level is done here (all earlier writes become visible first)
+__global__ void peer_signal_kernel(PeerCtx pc, const TreeState* st, int level, int phase) {
+  __threadfence_system();
+  const int r = threadIdx.x;
+  if (r < pc.world) {
+    volatile unsigned* fl = &pc.peers[r]->flags[phase][pc.rank];
+    *fl = peer_epoch(st, level, phase);
+  }
+}
+
+struct BestRec { unsigned long long key; int split_bin, dl; long long GL, HL; };
+
 // `base` points at forest row 0; the row of the tree being grown comes from the device-side counter
 __device__ __forceinline__ TreeOut tree_slice(const TreeOut& base, const TreeState* st, int max_nodes) {
   const size_t o = (size_t)st->tree_index * max_nodes;
@@ -45,6 +100,7 @@ __device__ __forceinline__ TreeOut tree_slice(const TreeOut& base, const TreeSta
 }
 
 __global__ void set_tree_index_kernel(TreeState* st, int idx) { st->tree_index = idx; }
+__global__ void init_state_kernel(TreeState* st) { st->tree_index = 0; st->round_seq = 0; st->peer_timeout = 0; }
 
 __global__ void round_init_kernel(TreeState* st, NodeArrays na, TreeOut to_base, int max_nodes, int n_rows,
                                   HistPlan* plan, int grid) {
@@ -89,20 +145,29 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
                                                                const uint8_t* __restrict__ feature_mask,
                                                                FeatBest* __restrict__ feat_best,
                                                                const int64_t* __restrict__ tail, TreeState* stw,
-                                                               int* __restrict__ group_cnt, int n_groups) {
+                                                               int* __restrict__ group_cnt, int n_groups, PeerCtx pc) {
   __shared__ long long sg[4], sh[4];
   __shared__ unsigned long long skf[4], skb[4];
   const int i = blockIdx.y;
+  if (pc.world > 1) {                       // every rank's level buffer must be complete before it is read
+    if (threadIdx.x == 0) peer_wait(pc, stw, 0, peer_epoch(stw, level, 0));
+    __syncthreads();
+  }
   if (blockIdx.x == 0 && i == 0)                        // housekeeping for the partition pass that follows
     for (int k = threadIdx.x; k < n_groups; k += blockDim.x) group_cnt[k] = 0;
   if (i >= st->lvl_count[level]) return;
-  const int feat = blockIdx.x;
+  const int feat = (pc.world > 1 ? pc.f0 : 0) + (int)blockIdx.x;
   const int nid = st->lvl_first[level] + i;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   long long Gt, Ht;
   if (level == 0) {
-    Gt = tail[0]; Ht = tail[1];
-    if (feat == 0 && tid == 0) { na.G[0] = Gt; na.H[0] = Ht; }
+    if (pc.world > 1) {                      // root totals: sum of the ranks' local totals (level buffer tail)
+      Gt = 0; Ht = 0;
+      for (int r = 0; r < pc.world; ++r) { Gt += __ldcv(pc.peer_level_buf[r] + 2 * (size_t)S); Ht += __ldcv(pc.peer_level_buf[r] + 2 * (size_t)S + 1); }
+    } else {
+      Gt = tail[0]; Ht = tail[1];
+    }
+    if (blockIdx.x == 0 && tid == 0) { na.G[0] = Gt; na.H[0] = Ht; }
   } else {
     Gt = na.G[nid]; Ht = na.H[nid];
   }
@@ -125,7 +190,16 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
     const int b = 2 * tid + k;
     v[k] = make_longlong2(0, 0);
     if (b < nb) {
-      v[k] = lb[b];
+      if (pc.world > 1) {                    // the fused collective: add this slice of every rank's histogram
+        long long ag = 0, ah = 0;
+        for (int r = 0; r < pc.world; ++r) {
+          const longlong2 q = __ldcv(reinterpret_cast<const longlong2*>(pc.peer_level_buf[r]) + (size_t)j * S + b0 + b);
+          ag += q.x; ah += q.y;
+        }
+        v[k] = make_longlong2(ag, ah);
+      } else {
+        v[k] = lb[b];
+      }
       if (par) { const longlong2 q = par[b]; v[k].x = q.x - v[k].x; v[k].y = q.y - v[k].y; }
       mine[b] = v[k];
     }
@@ -214,6 +288,27 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
   } while (0);
 }
 
+// peer mode, after the scan: every rank hands its best candidate per level node (over ITS feature slice)
+// to all ranks, then raises flag 1.  One CTA.
+__global__ void __launch_bounds__(256) peer_publish_kernel(PeerCtx pc, const TreeState* st, int level,
+                                                           const FeatBest* __restrict__ feat_best, int f) {
+  const int cnt = st->lvl_count[level];
+  for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+    PeerBest pb; pb.key = st->best_key[i]; pb.split_bin = 0; pb.dl = 0; pb.GL = 0; pb.HL = 0;
+    if (pb.key) {
+      const FeatBest* r = feat_best + (size_t)i * f + (0xFFFF - (int)(pb.key & 0xFFFFu));
+      pb.split_bin = r->split_bin; pb.dl = r->default_left; pb.GL = r->GL; pb.HL = r->HL;
+    }
+    for (int r = 0; r < pc.world; ++r) pc.peers[r]->tab[pc.rank][i] = pb;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if ((int)threadIdx.x < pc.world) {
+    volatile unsigned* fl = &pc.peers[threadIdx.x]->flags[1][pc.rank];
+    *fl = peer_epoch(st, level, 1);
+  }
+}
+
 struct SegCache {
   int begin[kMaxLevelNodes], count[kMaxLevelNodes];
 };
@@ -240,7 +335,32 @@ struct LevelCtx {
   cb_tree_params p;
   NodeArrays na;
   const int32_t* feat_pos;
+  PeerCtx pc;
 };
+
+// best split candidate of level node i: the local arg-max over features, or (peer mode) the arg-max over
+// the candidates every rank published for its feature slice (the key orders by gain, then lower feature)
+__device__ __forceinline__ BestRec get_best(const LevelCtx& c, int i) {
+  BestRec b; b.key = 0ull; b.split_bin = 0; b.dl = 0; b.GL = 0; b.HL = 0;
+  if (c.pc.world <= 1) {
+    b.key = __ldcg(&c.st->best_key[i]);
+    if (b.key) {
+      const FeatBest* r = c.feat_best + (size_t)i * c.f + (0xFFFF - (int)(b.key & 0xFFFFu));
+      b.split_bin = __ldcg(&r->split_bin); b.dl = __ldcg(&r->default_left); b.GL = __ldcg(&r->GL); b.HL = __ldcg(&r->HL);
+    }
+    return b;
+  }
+  int best_r = -1;
+  for (int r = 0; r < c.pc.world; ++r) {
+    const unsigned long long k = __ldcg(&c.pc.self->tab[r][i].key);
+    if (k > b.key) { b.key = k; best_r = r; }
+  }
+  if (best_r >= 0) {
+    const PeerBest* t = &c.pc.self->tab[best_r][i];
+    b.split_bin = __ldcg(&t->split_bin); b.dl = __ldcg(&t->dl); b.GL = __ldcg(&t->GL); b.HL = __ldcg(&t->HL);
+  }
+  return b;
+}
 
 // kind / split / leaf values of every node of the level, recomputed by whoever needs them
 __device__ void build_node_table(NodeTable& nt, const LevelCtx& c, bool want_leaves) {
@@ -248,7 +368,8 @@ __device__ void build_node_table(NodeTable& nt, const LevelCtx& c, bool want_lea
   const double dg = pow2neg(c.p.sg), dh = pow2neg(c.p.sh);
   for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
     const int nid = first + i;
-    const unsigned long long key = __ldg(&c.st->best_key[i]);
+    const BestRec br = get_best(c, i);
+    const unsigned long long key = br.key;
     const float bc = key ? __uint_as_float((unsigned)(key >> 32)) : 0.0f;
     const int bf = key ? 0xFFFF - (int)(key & 0xFFFFu) : -1;
     nt.begin[i] = c.na.begin[nid]; nt.count[i] = c.na.count[nid];
@@ -257,8 +378,7 @@ __device__ void build_node_table(NodeTable& nt, const LevelCtx& c, bool want_lea
     int sbin = 0, dl = 0;
     const long long G = c.na.G[nid], H = c.na.H[nid];
     if (bf >= 0) {
-      const FeatBest* r = c.feat_best + (size_t)i * c.f + bf;
-      GL = __ldg(&r->GL); HL = __ldg(&r->HL); sbin = __ldg(&r->split_bin); dl = __ldg(&r->default_left);
+      GL = br.GL; HL = br.HL; sbin = br.split_bin; dl = br.dl;
       valid = bc > 1e-6f && !(bc < c.p.gamma) && c.level < c.max_depth && HL != 0 && (H - HL) != 0;
     }
     if (valid) {
@@ -292,12 +412,11 @@ __device__ void finish_level(TreeState* st, const LevelCtx& c, const float* __re
   const int first = st->lvl_first[c.level], cnt = st->lvl_count[c.level];
   const double dg = pow2neg(c.p.sg), dh = pow2neg(c.p.sh);
   for (int i = threadIdx.x; i < cnt; i += blockDim.x) {      // validity again (cheap), 1 = splits
-    const unsigned long long key = __ldcg(&st->best_key[i]);
+    const BestRec br = get_best(c, i);
     int v = 0;
-    if (key) {
-      const float bc = __uint_as_float((unsigned)(key >> 32));
-      const int bf = 0xFFFF - (int)(key & 0xFFFFu);
-      const long long HL = __ldcg(&c.feat_best[(size_t)i * c.f + bf].HL), HR = c.na.H[first + i] - HL;
+    if (br.key) {
+      const float bc = __uint_as_float((unsigned)(br.key >> 32));
+      const long long HL = br.HL, HR = c.na.H[first + i] - HL;
       v = (bc > 1e-6f && !(bc < c.p.gamma) && c.level < c.max_depth && HL != 0 && HR != 0) ? 1 : 0;
     }
     s_child[i] = v;
@@ -332,11 +451,11 @@ __device__ void finish_level(TreeState* st, const LevelCtx& c, const float* __re
       segs->feat[i] = 0; segs->bin[i] = 0; segs->dl[i] = 0; segs->child[i] = -1;
       continue;
     }
-    const unsigned long long key = __ldcg(&st->best_key[i]);
+    const BestRec br = get_best(c, i);
+    const unsigned long long key = br.key;
     const int R = L + 1, bf = 0xFFFF - (int)(key & 0xFFFFu);
-    const FeatBest* r = c.feat_best + (size_t)i * c.f + bf;
-    const int sbin = __ldcg(&r->split_bin), dl = __ldcg(&r->default_left);
-    const long long GL = __ldcg(&r->GL), HL = __ldcg(&r->HL), GR = c.na.G[nid] - GL, HR = c.na.H[nid] - HL;
+    const int sbin = br.split_bin, dl = br.dl;
+    const long long GL = br.GL, HL = br.HL, GR = c.na.G[nid] - GL, HR = c.na.H[nid] - HL;
     to.left[nid] = L; to.right[nid] = R; to.parent[L] = nid; to.parent[R] = nid;
     to.split_index[nid] = bf; to.split_bin[nid] = sbin;
     to.split_cond[nid] = sbin >= 0 ? cuts[(size_t)bf * CB_CUT_STRIDE + sbin] : min_vals[bf];
@@ -400,6 +519,10 @@ __global__ void __launch_bounds__(256) part_level_flags_kernel(BinsView view, co
                                                                int* __restrict__ tile_cnt, int* __restrict__ group_cnt) {
   __shared__ NodeTable nt;
   __shared__ int wsum[8];
+  if (c.pc.world > 1) {                             // all ranks' candidates of this level must have arrived
+    if (threadIdx.x == 0) peer_wait(c.pc, stw, 1, peer_epoch(stw, c.level, 1));
+    __syncthreads();
+  }
   if (blockIdx.x == 0) {                            // the extra CTA (scheduled first): serial bookkeeping, overlapped with the tiles
     finish_level(stw, c, cuts, min_vals, tree_slice(to, stw, (1 << (c.max_depth + 1)) - 1), segs, nt.begin);
     return;
@@ -632,6 +755,10 @@ __global__ void __launch_bounds__(256) final_apply_kernel(BinsView view, const u
                                                           const float* __restrict__ min_vals, TreeOut to, LevelSegs* segs,
                                                           float* __restrict__ margin) {
   __shared__ NodeTable nt;
+  if (c.pc.world > 1) {
+    if (threadIdx.x == 0) peer_wait(c.pc, stw, 1, peer_epoch(stw, c.level, 1));
+    __syncthreads();
+  }
   if (blockIdx.x == 0) {
     finish_level(stw, c, cuts, min_vals, tree_slice(to, stw, (1 << (c.max_depth + 1)) - 1), segs, nt.begin);
     return;
@@ -681,6 +808,7 @@ __global__ void round_end_kernel(TreeState* st, int32_t* n_nodes_all) {
   if (threadIdx.x == 0) {
     n_nodes_all[st->tree_index] = st->n_nodes;
     st->tree_index += 1;
+    st->round_seq += 1;
   }
 }
 

@@ -69,6 +69,11 @@ class GpuTrainer:
         h = C.c_void_p()
         check(self.lib.cb_trainer_create(C.byref(self.cfg), C.byref(self.buffers), wp, wb, C.byref(h)))
         self.handle = h
+        self.peer_mode = False
+        self._sym_own = None
+        self._sym_peers = []
+        if self.world > 1 and os.environ.get("COBALT_MULTIGPU", "peer") != "nccl":
+            self._setup_peers()
         self.n_trees = 0
         self._level_views = {}
         self._graphs = {}
@@ -76,8 +81,54 @@ class GpuTrainer:
         self._launches_per_round = 0
         self.graph_error = None
 
+    def _setup_peers(self) -> None:
+        """Maps every rank's symmetric region into this process (CUDA IPC) and switches the library to the
+        fused form of the collective: no all-reduce calls, peers read each other's level buffers."""
+        dist = torch.distributed
+        rank = dist.get_rank(self.group)
+        need = C.c_size_t()
+        check(self.lib.cb_trainer_sym_bytes(C.byref(self.cfg), C.byref(need)))
+        own, handle = C.c_void_p(), (C.c_ubyte * 64)()
+        check(self.lib.cb_sym_alloc(need.value, C.byref(own), handle))
+        self._sym_own = own
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle), group=self.group)
+        regions = (C.c_void_p * self.world)()
+        for r in range(self.world):
+            if r == rank:
+                regions[r] = own.value
+            else:
+                p = C.c_void_p()
+                buf = (C.c_ubyte * 64).from_buffer_copy(handles[r])
+                check(self.lib.cb_sym_open(buf, C.byref(p)))
+                self._sym_peers.append(p)
+                regions[r] = p.value
+        check(self.lib.cb_trainer_set_peers(self.handle, rank, self.world, regions))
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)
+        self.peer_mode = True
+
+    def check_peers(self) -> None:
+        if self.peer_mode:
+            flag = C.c_int(0)
+            check(self.lib.cb_trainer_peer_status(self.handle, C.byref(flag)))
+            if flag.value:
+                raise _lib.CobaltError("a wait on a peer GPU timed out during training; results are invalid")
+
     def close(self):
         if getattr(self, "handle", None):
+            torch.cuda.synchronize()
+            self._graphs = {}                    # captured rounds reference this trainer's buffers
+            if self.peer_mode:
+                torch.cuda.synchronize()
+                try:
+                    torch.distributed.barrier(group=self.group)     # nobody may still be reading our region
+                except Exception:
+                    pass
+                for p in self._sym_peers:
+                    self.lib.cb_sym_close(p)
+                self.lib.cb_sym_free(self._sym_own)
+                self._sym_peers, self._sym_own, self.peer_mode = [], None, False
             self.lib.cb_trainer_destroy(self.handle)
             self.handle = None
 
@@ -101,7 +152,7 @@ class GpuTrainer:
         """One boosting round on the current stream.  tree_index < 0 continues the device-side counter."""
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         fm = None if feature_masks is None else C.c_void_p(feature_masks.data_ptr())
-        if self.world == 1:
+        if self.world == 1 or self.peer_mode:
             check(self.lib.cb_trainer_boost_round(self.handle, tree_index, fm, st))
         else:
             check(self.lib.cb_trainer_round_begin(self.handle, tree_index, fm, st))
@@ -198,6 +249,7 @@ class GpuTrainer:
 
     def forest_numpy(self) -> dict:
         """Padded [T][max_nodes] device arrays -> flat wire-format arrays on the host."""
+        self.check_peers()
         t = self.n_trees
         nn = self.n_nodes[:t].cpu().numpy()
         offs = np.zeros(t + 1, np.int64)

@@ -217,6 +217,22 @@ int cb_trainer_round_begin(cb_trainer* tr, int tree_index, const uint8_t* featur
 int cb_trainer_level_hist(cb_trainer* tr, int level, void* stream);
 int cb_trainer_level_split(cb_trainer* tr, int level, void* stream);
 int cb_trainer_round_end(cb_trainer* tr, void* stream);
+/* ---- row-sharded training over NVLink peer memory (the fused form of the path's one collective).
+ * Every rank allocates one "symmetric" region (cb_sym_alloc; size from cb_trainer_sym_bytes), exchanges the
+ * 64-byte IPC handles with its peers by any means (torch.distributed here), maps theirs (cb_sym_open) and hands
+ * all `world` addresses, own included at index `rank`, to cb_trainer_set_peers.  After that the level calls need
+ * no all-reduce in between: the scan kernel of each rank owns a slice of the features and adds that slice of every
+ * rank's local histogram straight out of peer memory, then publishes one candidate per node to all ranks; ranks
+ * synchronise through epoch flags in the regions.  cb_trainer_boost_round then runs a whole sharded round.
+ * No reference counterpart (the reference has no distributed code); replaces the NCCL all-reduce of the level buffer. */
+int cb_sym_alloc(size_t bytes, void** ptr, unsigned char* handle64);
+int cb_sym_open(const unsigned char* handle64, void** ptr);
+int cb_sym_close(void* ptr);
+int cb_sym_free(void* ptr);
+int cb_trainer_sym_bytes(const cb_train_config* cfg, size_t* bytes);
+int cb_trainer_set_peers(cb_trainer* tr, int rank, int world, void* const* regions);
+/* *timed_out != 0: a wait on a peer flag gave up (a peer died); results are then invalid.  Synchronises. */
+int cb_trainer_peer_status(cb_trainer* tr, int* timed_out);
 /* int64 buffer to sum over ranks after level_hist(level): pointer and element count */
 int cb_trainer_level_buffer(cb_trainer* tr, int level, int64_t** ptr, int64_t* n_values);
 /* introspection for parity tests: current row order u32 [n], histogram pool slot of a node */
