@@ -38,47 +38,84 @@ def _peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons sampled every 200 ms while the timed region runs."""
+    """SM clock + throttle reasons sampled every 20 ms while the timed region runs.
+
+    NVML in-process (the library nvidia-smi itself reads; handle opened BEFORE the timed region): starting an
+    `nvidia-smi -lms` process inside a 100-ms timed region enumerates all 8 GPUs of the box under a driver lock and
+    was seen to stall the launches of every rank.  Falls back to the nvidia-smi loop when pynvml is missing."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index: int):
-        self.lines, self.proc, self.index = [], None, index
+        self.samples, self.proc, self.index, self.nv, self.h, self.source = [], None, index, None, None, None
+        self._stop = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.replace(",", "").isdigit() else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.nv, self.source = pynvml, "nvml"
+        except Exception:
+            self.nv = None
+
+    def _poll_nvml(self):
+        nv = self.nv
+        bits = [nv.nvmlClocksThrottleReasonHwSlowdown, nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                nv.nvmlClocksThrottleReasonSwThermalSlowdown, nv.nvmlClocksThrottleReasonSwPowerCap]
+        while not self._stop.is_set():
+            try:
+                mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.samples.append((mhz, self.max_mhz, [bool(r & b) for b in bits]))
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def _poll_smi(self):
+        for l in self.proc.stdout:
+            parts = [x.strip() for x in l.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                self.samples.append((float(parts[0]), float(parts[1]),
+                                     [v.lower().startswith("active") for v in parts[2:6]]))
+            except ValueError:
+                continue
 
     def __enter__(self):
+        if self.nv is not None:
+            self.th = threading.Thread(target=self._poll_nvml, daemon=True)
+            self.th.start()
+            return self
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "200"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.th = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
+            self.source = "nvidia-smi"
+            self.th = threading.Thread(target=self._poll_smi, daemon=True)
             self.th.start()
         except Exception:
             self.proc = None
         return self
 
     def __exit__(self, *a):
-        if self.proc:
+        if self.nv is not None:
+            self._stop.set()
+            self.th.join(timeout=2)
+        elif self.proc:
             time.sleep(0.25)
             self.proc.terminate()
             self.th.join(timeout=2)
 
     def summary(self):
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for l in self.lines:
-            parts = [x.strip() for x in l.split(",")]
-            if len(parts) < 6:
-                continue
-            try:
-                sm.append(float(parts[0])); mx.append(float(parts[1]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, parts[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        sm.sort()
+        sm = sorted(x[0] for x in self.samples)
+        mx = [x[1] for x in self.samples]
+        reasons = {nm for x in self.samples for nm, on in zip(self.NAMES, x[2]) if on}
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": self.source}
 
 
 def _dist_init(n_gpus: int):
@@ -328,7 +365,10 @@ def run_ours(args):
                                                 "max_depth": DEPTH, "rounds_timed": args.steps, "total_bins": S,
                                                 "l2_policy": "inputs larger than L2 (352 MB binned matrix vs 126 MB L2)" if world == 1 else
                                                 "binned shard may fit L2 at N>=4 (strong scaling of a 352 MB matrix)",
-                                                "parallelism": f"rows sharded x{world}, NCCL allreduce of per-level histograms"},
+                                                "parallelism": (f"rows sharded x{world}, " + (
+                                                    "per-level histograms summed over NVLink peer memory inside the split scan"
+                                                    if tr.peer_mode else "NCCL allreduce of per-level histograms"))
+                                                if world > 1 else "single GPU"},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clk.summary(), "scoring": scoring, "prep_ms": round(t_prep, 2), "train_auc_200k": auc}
         print(json.dumps(line), file=_OUT, flush=True)
@@ -389,7 +429,7 @@ def _quiet_stdout():
 
 
 def main():
-    global _OUT
+    global _OUT, DEPTH, WORKLOAD
     _OUT = _quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -397,6 +437,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rows", type=int, default=N_ROWS)
+    ap.add_argument("--depth", type=int, default=DEPTH, help="tree depth; 8 with --rows 20000000 --gpus 8 is configs[3]")
     ap.add_argument("--e2e-rounds", type=int, default=ROUNDS_CFG)
     ap.add_argument("--score-rows", type=int, default=SCORE_ROWS)
     ap.add_argument("--score-steps", type=int, default=3)
@@ -406,6 +447,10 @@ def main():
     ap.add_argument("--no-scoring", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    if args.depth != DEPTH or args.rows != N_ROWS:
+        DEPTH = args.depth
+        WORKLOAD = (f"synthetic Lending-Club schema {args.rows / 1e6:g}M x {N_FEAT}, 256 bins, depth {DEPTH}"
+                    + (" (BASELINE.json configs[3])" if (args.rows, DEPTH) == (20_000_000, 8) else ""))
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     if args.impl == "reference":
         run_reference(args)

@@ -71,7 +71,7 @@ __device__ __forceinline__ void peer_wait(const PeerCtx& pc, TreeState* st, int 
     volatile unsigned* fl = &pc.self->flags[phase][r];
     unsigned long long spins = 0;
     while ((int)(*fl - epoch) < 0) {
-      if (++spins > (1ull << 24)) { st->peer_timeout = 1; break; }
+      if (++spins > (1ull << 25)) { st->peer_timeout = 1; break; }
       __nanosleep(64);
     }
   }
