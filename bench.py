@@ -317,7 +317,8 @@ def run_ours(args):
         visits = args.score_rows * SCORE_TREES * DEPTH
         sc = {"metric": "scoring rows/s", "value": round(rows_s, 0), "ms_per_pass": round(ms_s, 3),
               "workload": f"{args.score_rows} rows x {N_FEAT}, {SCORE_TREES} trees depth {DEPTH} (configs[4])",
-              "roofline": {"kernel": "predict_heap_kernel", "bound": "hbm (contract); binding resource is shared-memory lookups + ALU issue", "achieved": round(sbytes / (ms_s / 1e3) / 1e9, 1),
+              "roofline": {"kernel": "bin_pack_kernel + predict_q8_kernel" if booster._device_q8(dev) is not None else "predict_heap_kernel",
+                           "bound": "hbm (contract); binding resource is shared-memory lookups + ALU issue", "achieved": round(sbytes / (ms_s / 1e3) / 1e9, 1),
                            "peak": peak, "unit": "GB/s", "frac": round(sbytes / (ms_s / 1e3) / 1e9 / peak, 4),
                            "traffic": None},
               "node_visits_per_s": round(visits / (ms_s / 1e3), 0)}

@@ -100,6 +100,9 @@ _SIGS = {
     "cb_predict": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _I, _F, _VP, _VP, _VP]),
     "cb_predict_heap_plan": (C.c_int, [_I, _I, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "cb_predict_heap": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _I, _I, _F, _VP, _VP, _VP]),
+    "cb_predict_q8_plan": (C.c_int, [_I, _I, _I64, C.POINTER(C.c_int), C.POINTER(C.c_uint32)]),
+    "cb_bin_rows_u8": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _VP, _I64, _VP]),
+    "cb_predict_q8": (C.c_int, [_VP, _I64, _I, _I64, _VP, _I, _I, _F, C.c_uint32, _VP, _VP, _VP]),
     "cb_trainer_workspace_bytes": (C.c_int, [C.POINTER(TrainConfig), C.POINTER(_SZ)]),
     "cb_trainer_create": (C.c_int, [C.POINTER(TrainConfig), C.POINTER(TrainBuffers), _VP, _SZ, C.POINTER(_VP)]),
     "cb_trainer_destroy": (None, [_VP]),

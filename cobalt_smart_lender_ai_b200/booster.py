@@ -5,6 +5,7 @@ entry point.  Mirrors the parts of ``xgboost.Booster`` the reference touches:
 from __future__ import annotations
 
 import math
+import os
 
 import numpy as np
 import torch
@@ -85,6 +86,45 @@ def heap_forest(tree_offsets, left, right, split_index, split_cond, default_left
     return thr, meta, np.ascontiguousarray(cond[cur]), depth
 
 
+def q8_forest(thr: np.ndarray, meta: np.ndarray, leaf: np.ndarray, depth: int, n_features: int, plane_base: int = 0):
+    """heap_forest output -> what cb_predict_q8 needs: the forest's threshold table (per feature: distinct split_cond
+    values ascending, then +inf) for cb_bin_pack_u8, and the u32 forest [T, 2 << depth] (1-based heap: nodes, then
+    leaves).  "x < t_k" <=> "code <= k" with code = number of thresholds <= x.  None when a feature has more than
+    254 distinct thresholds or the feature offsets do not fit 16 bits."""
+    T, NI = thr.shape
+    NL = 1 << depth
+    if n_features > 255:
+        return None
+    feat = (meta & 0x7FFF).astype(np.int64)
+    dl = (meta >> 15).astype(np.int64)
+    # internal (real) nodes are those whose two subtrees differ; pass-through nodes carry thr 0 / meta 0 and may go
+    # either way, so they simply take part as "feature 0, threshold 0.0" comparisons when they are not filtered here
+    cuts = np.full((n_features, 256), np.inf, np.float32)
+    n_cuts = np.ones(n_features, np.int32)
+    kidx = np.zeros((T, NI), np.int64)
+    for j in range(n_features):
+        sel = feat == j
+        if not sel.any():
+            continue
+        vals = thr[sel]
+        if np.isnan(vals).any():
+            return None
+        u, inv = np.unique(vals, return_inverse=True)        # -0.0 == 0.0 collapse, like the f32 compare
+        if len(u) > 254:
+            return None
+        cuts[j, :len(u)] = u
+        n_cuts[j] = len(u) + 1                               # + the +inf sentinel: codes run 0 .. len(u)
+        kidx[sel] = inv.reshape(-1)
+    span = kidx + dl                                         # plane 1 (default left) holds code + 1, missing = 0
+    off = plane_base + (dl * n_features + feat) * 128        # shared-window address of the (plane, feature) column
+    if off.max(initial=0) + 127 > 0xFFFF or span.max(initial=0) > 255:
+        return None
+    words = np.zeros((T, 2 * NL), np.uint32)
+    words[:, 1:NL] = ((span << 16) | off).astype(np.uint32)
+    words[:, NL:] = np.ascontiguousarray(leaf, np.float32).view(np.uint32)
+    return cuts, n_cuts, words
+
+
 class Booster:
     def __init__(self, forest: dict, n_features: int, feature_names=None, base_score: float = 0.5,
                  attributes: dict | None = None):
@@ -149,8 +189,13 @@ class Booster:
         """X: CUDA f32 [n, n_features].  Returns p (or the margin) as a CUDA f32 [n] tensor."""
         if X.shape[1] != self.n_features:
             raise ValueError(f"Feature shape mismatch, expected: {self.n_features}, got {X.shape[1]}")
-        heap = self._device_heap(X.device)
-        if heap is not None:
+        q8 = self._device_q8(X.device)
+        heap = self._device_heap(X.device) if q8 is None else None
+        if q8 is not None:
+            cuts, n_cuts, words, depth, plane_base = q8
+            m, p = ops.predict_q8(X, cuts, n_cuts, words, depth, plane_base, base_margin_of(self.base_score),
+                                  self.num_boosted_rounds(), want_margin=output_margin, want_proba=not output_margin)
+        elif heap is not None:
             nodes_h, leaf, depth = heap
             m, p = ops.predict_heap(X, nodes_h, leaf, depth, base_margin_of(self.base_score),
                                     self.num_boosted_rounds(), want_margin=output_margin, want_proba=not output_margin)
@@ -159,6 +204,33 @@ class Booster:
             m, p = ops.predict(X, nodes, toff, base_margin_of(self.base_score), want_margin=output_margin,
                                want_proba=not output_margin)
         return m if output_margin else p
+
+    def _device_q8(self, device):
+        """Quantised-input form of the forest (the fastest scorer), or None when it does not apply."""
+        key = "q8:" + str(device)
+        if key not in self._dev_cache:
+            self._dev_cache[key] = None
+            fo = self.forest
+            h = None
+            if os.environ.get("COBALT_PREDICT", "q8") == "q8" and self.n_features <= 255:
+                h = heap_forest(fo["tree_offsets"], fo["left"], fo["right"], fo["split_index"], fo["split_cond"],
+                                fo["default_left"])
+            if h is not None:
+                thr, meta, leaf, depth = h
+                with torch.cuda.device(device):
+                    chunk, plane_base = ops.predict_q8_plan(self.n_features, depth)
+                q = q8_forest(thr, meta, leaf, depth, self.n_features, plane_base) if chunk >= 8 else None
+                if q is not None:
+                    cuts, n_cuts, words = q
+                    T = words.shape[0]
+                    Tp = (T + chunk - 1) // chunk * chunk
+                    pad = np.zeros((Tp - T, words.shape[1]), np.uint32)
+                    pad[:, 1:1 << depth] = plane_base                # padding trees: valid addresses, leaves 0.0
+                    words = np.concatenate([words, pad], 0)
+                    with torch.cuda.device(device):
+                        self._dev_cache[key] = (torch.from_numpy(cuts).to(device), torch.from_numpy(n_cuts).to(device),
+                                                torch.from_numpy(words.view(np.int32)).to(device), depth, plane_base)
+        return self._dev_cache[key]
 
     def _device_heap(self, device):
         key = "heap:" + str(device)

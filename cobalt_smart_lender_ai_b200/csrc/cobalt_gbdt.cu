@@ -438,6 +438,111 @@ int cb_predict_heap(const float* X, int64_t n, int f, int64_t ldx, const uint64_
   return CB_OK;
 }
 
+// quantised-input scoring: CTAs of 128 rows; as many per SM as shared memory allows (tile + staging are fixed,
+// the two tree-chunk buffers take what is left, >= 8 trees each)
+constexpr int kQ8Ilp = 16;                 // trees in flight per thread
+static int q8_chunk_trees(const DeviceInfo& di, int f, int depth, int64_t ldc, int* smem_bytes) {
+  const int64_t TB = (int64_t)8 << depth;
+  const int64_t planes = ((int64_t)2 * f * 128 + 127) & ~(int64_t)127;
+  const int64_t staging = (ldc * 128 + 127) & ~(int64_t)127;     // aliases the ring
+  const int64_t per_sm = (int64_t)di.smem_optin + 1024;          // opt-in per-CTA limit + its 1 KB reserve = the SM's carve-out
+  for (int k = 4; k >= 1; --k) {
+    const int64_t avail = per_sm / k - 1024 - 256 - planes;
+    int chunk = (int)std::min<int64_t>(avail / (kQ8Stages * TB), 64) & ~(kQ8Ilp - 1);
+    if (chunk >= kQ8Ilp && (int64_t)kQ8Stages * chunk * TB >= staging) {
+      if (smem_bytes) *smem_bytes = (int)(planes + kQ8Stages * chunk * TB + 8 * (kQ8Stages + 1));
+      return chunk;
+    }
+  }
+  return 0;
+}
+
+static int q8_plane_base(const DeviceInfo& di, uint32_t* base) {
+  static std::mutex mu;
+  static uint32_t cached[64];
+  static bool have[64];
+  std::lock_guard<std::mutex> lock(mu);
+  const int d = di.device & 63;
+  if (!have[d]) {
+    uint32_t* dv = nullptr;
+    CB_CUDA(cudaMalloc(&dv, sizeof(uint32_t)));
+    smem_base_probe_kernel<<<1, 1, 1024>>>(dv);
+    cudaError_t e = cudaMemcpy(&cached[d], dv, sizeof(uint32_t), cudaMemcpyDeviceToHost);
+    cudaFree(dv);
+    if (e != cudaSuccess) return fail(CB_ERR_CUDA, "cb_predict_q8_plan: probe failed: %s", cudaGetErrorString(e));
+    have[d] = true;
+  }
+  *base = cached[d];
+  return CB_OK;
+}
+
+int cb_predict_q8_plan(int n_features, int depth, int64_t ldc, int* chunk_trees, uint32_t* plane_base) {
+  if (!chunk_trees || !plane_base || n_features <= 0 || n_features > 255 || depth < 1 || depth > 10 || ldc < n_features ||
+      (ldc & 3) || !((ldc >> 2) & 1))
+    return fail(CB_ERR_INVALID, "cb_predict_q8_plan: need 1..255 features, depth 1..10 and ldc = 4 * odd >= n_features");
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  if ((rc = q8_plane_base(di, plane_base))) return rc;
+  *chunk_trees = q8_chunk_trees(di, n_features, depth, ldc, nullptr);
+  if (*chunk_trees < kQ8Ilp || (*plane_base & 127u) || *plane_base + 2u * (uint32_t)n_features * 128u > 0x10000u)
+    return fail(CB_ERR_UNSUPPORTED, "cb_predict_q8: %d features at depth %d do not fit shared memory", n_features, depth);
+  return CB_OK;
+}
+
+int cb_bin_rows_u8(const float* X, int64_t n, int f, int64_t ldx, const float* cuts, const int32_t* n_cuts, uint8_t* codes,
+                   int64_t ldc, void* stream) {
+  if (n == 0) return CB_OK;
+  if (!X || !cuts || !n_cuts || !codes || n < 0 || f <= 0 || ldx < f || ldc < f)
+    return fail(CB_ERR_INVALID, "cb_bin_rows_u8: bad arguments");
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  const int slabs = ceil_div(f, 32);
+  // about 4 CTAs per SM and slab, at least 256 rows each: the table load is amortised over the CTA's rows
+  int64_t rows_per_cta = std::max<int64_t>(256, ceil_div(n, (int64_t)di.sm_count * 4));
+  rows_per_cta = (rows_per_cta + 31) & ~(int64_t)31;
+  bin_rows_q8_kernel<<<dim3((unsigned)ceil_div(n, rows_per_cta), slabs), 256, 0, (cudaStream_t)stream>>>(
+      X, n, f, ldx, cuts, n_cuts, codes, ldc, (int)rows_per_cta);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+int cb_predict_q8(const uint8_t* codes, int64_t n, int f, int64_t ldc, const uint32_t* forest, int n_trees, int depth,
+                  float base_margin, uint32_t plane_base, float* out_margin, float* out_proba, void* stream) {
+  if (n == 0) return CB_OK;
+  if (!codes || !forest || n < 0 || f <= 0 || f > 255 || ldc < f || (ldc & 3) || !((ldc >> 2) & 1) || n_trees < 0 || depth < 1 ||
+      depth > 10 || (!out_margin && !out_proba))
+    return fail(CB_ERR_INVALID, "cb_predict_q8: bad arguments");
+  if ((reinterpret_cast<uintptr_t>(codes) | reinterpret_cast<uintptr_t>(forest)) & 15)
+    return fail(CB_ERR_INVALID, "cb_predict_q8: codes and forest must be 16-byte aligned");
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  int smem = 0;
+  const int chunk = q8_chunk_trees(di, f, depth, ldc, &smem);
+  if (chunk < 8) return fail(CB_ERR_UNSUPPORTED, "cb_predict_q8: %d features at depth %d do not fit shared memory", f, depth);
+  auto launch = [&](auto kernel) -> int {
+    CB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, di.smem_optin - 1024));
+    kernel<<<ceil_div(n, 128), 128, smem, (cudaStream_t)stream>>>(codes, n, f, ldc, forest, n_trees, chunk, base_margin,
+                                                                  plane_base, out_margin, out_proba);
+    CB_LAUNCH_CHECK();
+    return CB_OK;
+  };
+  switch (depth) {
+    case 1: return launch(predict_q8_kernel<kQ8Ilp, 1>);
+    case 2: return launch(predict_q8_kernel<kQ8Ilp, 2>);
+    case 3: return launch(predict_q8_kernel<kQ8Ilp, 3>);
+    case 4: return launch(predict_q8_kernel<kQ8Ilp, 4>);
+    case 5: return launch(predict_q8_kernel<kQ8Ilp, 5>);
+    case 6: return launch(predict_q8_kernel<kQ8Ilp, 6>);
+    case 7: return launch(predict_q8_kernel<kQ8Ilp, 7>);
+    case 8: return launch(predict_q8_kernel<kQ8Ilp, 8>);
+    case 9: return launch(predict_q8_kernel<kQ8Ilp, 9>);
+    default: return launch(predict_q8_kernel<kQ8Ilp, 10>);
+  }
+}
+
 // ---------------------------------------------------------------------------- trainer
 struct cb_trainer_s {
   cb_train_config cfg;

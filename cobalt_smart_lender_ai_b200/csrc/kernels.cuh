@@ -676,4 +676,220 @@ __global__ void __launch_bounds__(256) predict_heap_kernel(const float* __restri
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Scoring on quantised inputs.  A split "x < thr" only ever compares x with one of the forest's own
+// thresholds, so a row can be reduced once to one byte per feature -- code = number of that feature's
+// distinct thresholds <= x (K2's binary search against the forest's threshold table), 255 = missing --
+// and "x < t_k" becomes "code <= k", bit for bit the same decision.  That makes a node 4 bytes instead
+// of 8 and a feature value 1 byte instead of 4: 2 shared-memory wavefronts per (warp, level) instead of
+// ~3.75, and 2 ALU-pipe instructions instead of 5 (the two resources the f32 kernel is bound by).
+//   codes  : row major [n][ldc] bytes, ldc = 4 * odd: a tile of 128 rows is ONE contiguous block, fetched
+//            with one bulk copy (TMA) and transposed from shared to shared memory without bank conflicts.
+//   tile   : two byte planes [f][128]: plane 0 holds the codes (missing = 255, never <= span), plane 1
+//            holds code + 1 with missing = 0 (always <= span): default-left nodes read plane 1, so the
+//            missing rule costs no instruction.  Row r of a column sits at byte 4 * (r % 32) + r / 32:
+//            a warp's 32 rows are in 32 different banks whatever features its lanes look at.
+//   node   : u32 = span << 16 | byte offset of (plane, feature); go left iff (code << 16) <= node.
+//            Heap order, 1-based: tree t occupies 8 << depth bytes, node i at byte 4i, children at
+//            8i / 8i + 4, and the 2^depth leaves (f32) simply follow as i = 2^depth .. 2^(depth+1)-1:
+//            after `depth` steps the walk address IS the leaf address.  A level of <= 32 nodes is
+//            <= 32 consecutive words: node fetches are conflict free up to depth 6.
+// K2 for scoring: codes of a 32-feature slab of X, row major.  The slab's threshold table sits in shared memory
+// (32 x 257 floats: the odd stride spreads the lanes' probes over the banks), lane = feature, so X is read in
+// 128-byte row segments and the 8 probes of the (branch-free, fixed-length) binary search never leave the SM --
+// the general K2 kernel probes the table through L1 with 32 different sectors per warp load and takes 2.5x longer.
+__global__ void __launch_bounds__(256) bin_rows_q8_kernel(const float* __restrict__ X, int64_t n, int f, int64_t ldx,
+                                                          const float* __restrict__ cuts, const int32_t* __restrict__ n_cuts,
+                                                          uint8_t* __restrict__ codes, int64_t ldc, int rows_per_cta) {
+  __shared__ float tab[32 * 257];
+  const int c0 = blockIdx.y * 32;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < 32 * 256; i += 256) {
+    const int cf = i >> 8, k = i & 255;
+    tab[cf * 257 + k] = (c0 + cf < f) ? __ldg(cuts + (size_t)(c0 + cf) * CB_CUT_STRIDE + k) : 0.0f;
+  }
+  __syncthreads();
+  const int c = c0 + lane;
+  const bool on = c < f;
+  const int nc = on ? __ldg(n_cuts + c) : 1;
+  const float* my = tab + lane * 257;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta, r1 = min(n, r0 + rows_per_cta);
+  for (int64_t rb = r0 + warp * 4; rb < r1; rb += 32) {       // 8 warps x 4 rows in flight
+    float x[4];
+    int lo[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t r = min(rb + u, r1 - 1);
+      x[u] = on ? __ldg(X + r * ldx + c) : 0.0f;
+      lo[u] = 0;
+    }
+#pragma unroll
+    for (int s = 128; s > 0; s >>= 1) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int probe = lo[u] + s;
+        if (probe <= nc && my[probe - 1] <= x[u]) lo[u] = probe;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t r = rb + u;
+      if (on && r < r1) {
+        uint32_t code = (uint32_t)(lo[u] == nc ? nc - 1 : lo[u]);   // same clamp as K2 (never taken with a +inf sentinel)
+        if (x[u] != x[u]) code = CB_MISSING_BIN;
+        codes[r * ldc + c] = (uint8_t)code;
+      }
+    }
+  }
+}
+
+// shared-window address of the dynamic shared memory of a kernel without static shared memory
+__global__ void smem_base_probe_kernel(uint32_t* out) {
+  extern __shared__ __align__(128) uint8_t probe_s[];
+  *out = (uint32_t)__cvta_generic_to_shared(probe_s);
+}
+
+constexpr int kQ8Stages = 4;               // tree-chunk buffers in flight: a chunk is walked faster than a bulk copy lands
+// one level of one tree walk.  a = shared address of the node; children of the node at S + 4i are at
+// 2 * (S + 4i) - S (+ 4): cl = -S, cr = 4 - S.  The shift and both address updates run on the FMA pipe; the ALU
+// pipe (half rate) only sees the offset mask/or and the compare.
+__device__ __forceinline__ void q8_step(uint32_t& a, uint32_t x, uint32_t q, uint32_t two, uint32_t cl, uint32_t cr) {
+  asm("{\n\t.reg .pred pl;\n\t.reg .u32 xs;\n\t"
+      "mul.lo.u32 xs, %1, 65536;\n\t"
+      "setp.le.u32 pl, xs, %2;\n\t"
+      "@pl mad.lo.u32 %0, %0, %3, %4;\n\t"
+      "@!pl mad.lo.u32 %0, %0, %3, %5;\n\t}"
+      : "+r"(a)
+      : "r"(x), "r"(q), "r"(two), "r"(cl), "r"(cr));
+}
+
+template <int ILP, int DEPTH>
+__global__ void __launch_bounds__(128) predict_q8_kernel(const uint8_t* __restrict__ codes, int64_t n, int f, int64_t ldc,
+                                                         const uint32_t* __restrict__ forest, int n_trees,
+                                                         int chunk_trees, float base_margin, uint32_t plane_base,
+                                                         float* __restrict__ out_margin, float* __restrict__ out_proba) {
+  // planes [2][f][128] | ring of kQ8Stages tree-chunk buffers | mbarriers.  The row-major staging copy of the tile
+  // ([128][ldc]) lives in the ring too and is dead before the first chunk is requested.  No static shared memory:
+  // the planes start at the bottom of the CTA's shared window, whose address (plane_base, cb_predict_q8_plan) is
+  // already added to every node's offset field, so "(node & 0xFFFF) | row byte" IS the shared address of the code.
+  extern __shared__ __align__(128) uint8_t q8s[];
+  if ((uint32_t)__cvta_generic_to_shared(q8s) != plane_base) __trap();   // forest was laid out for another window
+  constexpr int R = 128;
+  constexpr int depth = DEPTH;
+  constexpr uint32_t TB = 8u << DEPTH;              // bytes per tree
+  const uint32_t plane_b = (uint32_t)f * R;
+  uint8_t* buf0 = q8s + ((2 * plane_b + 127) & ~127u);
+  uint8_t* stage = buf0;
+  const uint32_t buf_b = (uint32_t)chunk_trees * TB;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(buf0 + (size_t)kQ8Stages * buf_b);
+  const int n_chunks = (n_trees + chunk_trees - 1) / chunk_trees;   // the array is padded to whole chunks
+  const int64_t row0 = (int64_t)blockIdx.x * R;
+  const int nrow = (int)min((int64_t)R, n - row0);
+  const bool bulk_tile = nrow == R;                 // a partial last tile is copied by hand (size not a multiple of 16)
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k <= kQ8Stages; ++k) mbar_init(&bars[k], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  auto issue = [&](int c) {
+    uint64_t* bar = &bars[c % kQ8Stages];
+    mbar_expect_tx(bar, buf_b);
+    bulk_g2s(buf0 + (size_t)(c % kQ8Stages) * buf_b, reinterpret_cast<const uint8_t*>(forest) + (size_t)c * buf_b, buf_b, bar);
+  };
+  if (threadIdx.x == 0 && bulk_tile) {
+    mbar_expect_tx(&bars[kQ8Stages], (uint32_t)ldc * R);
+    bulk_g2s(stage, codes + row0 * ldc, (uint32_t)ldc * R, &bars[kQ8Stages]);
+  }
+  const uint32_t r = threadIdx.x;
+  const uint32_t pr = 4u * (r & 31u) + (r >> 5);     // this row's byte inside a feature column
+  if (bulk_tile) {
+    mbar_wait(&bars[kQ8Stages], 0u);
+  } else {
+    const int wpr = (int)(ldc >> 2);
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(codes + row0 * ldc);
+    for (int i = threadIdx.x; i < nrow * wpr; i += R) reinterpret_cast<uint32_t*>(stage)[i] = __ldg(src + i);
+    __syncthreads();
+  }
+  if ((int)r < nrow) {                               // transpose: lane = row; ldc / 4 is odd, so the word reads spread over the banks
+    const uint32_t* mine = reinterpret_cast<const uint32_t*>(stage + (size_t)r * ldc);
+    for (int w = 0; 4 * w < f; ++w) {
+      const uint32_t v = mine[w];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int c = 4 * w + j;
+        if (c < f) {
+          const uint32_t b = (v >> (8 * j)) & 255u;
+          q8s[(uint32_t)c * R + pr] = (uint8_t)b;
+          q8s[plane_b + (uint32_t)c * R + pr] = (uint8_t)(b + 1u);   // 255 (missing) wraps to 0
+        }
+      }
+    }
+  }
+  __syncthreads();                                   // planes complete, staging dead: the ring may fill
+  if (threadIdx.x == 0) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    for (int c = 0; c < kQ8Stages && c < n_chunks; ++c) issue(c);
+  }
+  float m = base_margin;
+  for (int c = 0; c < n_chunks; ++c) {
+    const uint8_t* buf = buf0 + (size_t)(c % kQ8Stages) * buf_b;
+    mbar_wait(&bars[c % kQ8Stages], (uint32_t)((c / kQ8Stages) & 1));
+    const int ct = min(chunk_trees, n_trees - c * chunk_trees);
+    {
+      // Every thread walks, also those past the last row of a partial tile (their codes are whatever the planes
+      // hold; all addresses stay inside the planes and the tree).  Walk addresses are absolute shared-memory
+      // addresses, so a visit is: load node, mask|or, load code, shift, compare, one of two multiply-adds.
+      uint32_t two;
+      asm volatile("mov.u32 %0, 2;" : "=r"(two));  // a register on purpose: keeps the updates IMADs (FMA pipe)
+      const uint32_t sbuf = (uint32_t)__cvta_generic_to_shared(buf);
+      int t = 0;
+      for (; t + ILP <= ct; t += ILP) {
+        uint32_t a[ILP], cl[ILP], cr[ILP];
+#pragma unroll
+        for (int k = 0; k < ILP; ++k) {
+          const uint32_t S = sbuf + (uint32_t)(t + k) * TB;
+          a[k] = S + 4u; cl[k] = 0u - S; cr[k] = 4u - S;
+        }
+#pragma unroll 1                                  // one level at a time: unrolled, ptxas walks tree after tree (no ILP)
+        for (int d = 0; d < depth; ++d) {
+          uint32_t q[ILP], x[ILP];
+#pragma unroll
+          for (int k = 0; k < ILP; ++k) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(q[k]) : "r"(a[k]));
+#pragma unroll
+          for (int k = 0; k < ILP; ++k) asm volatile("ld.shared.u8 %0, [%1];" : "=r"(x[k]) : "r"((q[k] & 0xFFFFu) | pr));
+#pragma unroll
+          for (int k = 0; k < ILP; ++k) q8_step(a[k], x[k], q[k], two, cl[k], cr[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < ILP; ++k) {
+          float lv;
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(lv) : "r"(a[k]));
+          m = __fadd_rn(m, lv);
+        }
+      }
+      for (; t < ct; ++t) {
+        uint32_t a0 = (uint32_t)t * TB + 4u;
+        const uint32_t cl0 = 0u - (uint32_t)t * TB;
+#pragma unroll 1
+        for (int d = 0; d < depth; ++d) {
+          const uint32_t q0 = *reinterpret_cast<const uint32_t*>(buf + a0);
+          const uint32_t x0 = q8s[((q0 & 0xFFFFu) | pr) - plane_base];
+          a0 = 2u * a0 + cl0 + (((x0 << 16) <= q0) ? 0u : 4u);
+        }
+        m = __fadd_rn(m, *reinterpret_cast<const float*>(buf + a0));
+      }
+    }
+    __syncthreads();                               // every thread is done with this buffer
+    if (threadIdx.x == 0 && c + kQ8Stages < n_chunks) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      issue(c + kQ8Stages);
+    }
+  }
+  if ((int)r < nrow) {
+    if (out_margin) out_margin[row0 + r] = m;
+    if (out_proba) out_proba[row0 + r] = spec_sigmoid(m);
+  }
+}
+
 }  // namespace cb

@@ -225,3 +225,41 @@ def predict_heap(X: torch.Tensor, nodes: torch.Tensor, leaf: torch.Tensor, depth
     check(_lib.load().cb_predict_heap(_ptr(X), n, f, _ld(X), _ptr(nodes), _ptr(leaf), int(n_trees), depth,
                                       float(base_margin), _ptr(m), _ptr(p), _stream()))
     return m, p
+
+
+def q8_ldc(n_features: int) -> int:
+    """Row stride of the code matrix cb_predict_q8 wants: the smallest 4 * odd >= n_features."""
+    w = (n_features + 3) // 4
+    return 4 * (w | 1)
+
+
+def predict_q8_plan(n_features: int, depth: int) -> tuple[int, int]:
+    """(trees per shared-memory chunk, shared-window address of the code planes) of the quantised-input scorer;
+    (0, 0) = does not fit / not applicable."""
+    if n_features > 255 or depth > 10:
+        return 0, 0
+    c, b = C.c_int(0), C.c_uint32(0)
+    rc = _lib.load().cb_predict_q8_plan(n_features, depth, q8_ldc(n_features), C.byref(c), C.byref(b))
+    return (c.value, b.value) if rc == 0 else (0, 0)
+
+
+def predict_q8(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, forest: torch.Tensor, depth: int,
+               plane_base: int, base_margin: float, n_trees: int, want_margin: bool = False, want_proba: bool = True,
+               batch_rows: int = 1 << 19):
+    """K8 on quantised inputs: K2 against the forest's threshold table, then the byte-tile walk.  Rows go through
+    in batches so that the code matrix (80 MB per batch) is still in L2 when the walk reads it."""
+    _need_cuda(X, cuts, n_cuts, forest)
+    assert X.dtype == torch.float32 and X.stride(1) == 1
+    n, f = X.shape
+    ldc = q8_ldc(f)
+    m = torch.empty(n, dtype=torch.float32, device=X.device) if want_margin else None
+    p = torch.empty(n, dtype=torch.float32, device=X.device) if want_proba else None
+    lib = _lib.load()
+    codes = torch.empty((min(n, batch_rows), ldc), dtype=torch.uint8, device=X.device)
+    for r0 in range(0, n, batch_rows):
+        r1 = min(n, r0 + batch_rows)
+        check(lib.cb_bin_rows_u8(_ptr(X[r0:r1]), r1 - r0, f, _ld(X), _ptr(cuts), _ptr(n_cuts), _ptr(codes), ldc, _stream()))
+        check(lib.cb_predict_q8(_ptr(codes), r1 - r0, f, ldc, _ptr(forest), int(n_trees), depth, float(base_margin),
+                                int(plane_base), _ptr(m[r0:r1]) if m is not None else None,
+                                _ptr(p[r0:r1]) if p is not None else None, _stream()))
+    return m, p

@@ -212,9 +212,11 @@ def make_lending(n: int, f: int, seed: int = DATA_SEED, row_offset: int = 0, dev
     return X, y, [c[0] for c in cols]
 
 
-def random_forest_like(n_trees: int, depth: int, f: int, seed: int = 78, device="cpu"):
+def random_forest_like(n_trees: int, depth: int, f: int, seed: int = 78, device="cpu", grid: int = 100):
     """A random full-depth forest in the wire format (for scoring benchmarks without training).
-    Thresholds are drawn around the schema's typical values so both branches are exercised."""
+    Thresholds are drawn around the schema's typical values so both branches are exercised, on a grid of
+    2 * grid + 1 values per feature: a forest grown by the 256-bin hist method can only split at its <= 255 cut
+    values per feature, and the scorer relies on that (grid=0: continuous thresholds)."""
     g = torch.Generator().manual_seed(seed)
     n_int = (1 << depth) - 1
     n_nodes = (1 << (depth + 1)) - 1
@@ -227,7 +229,10 @@ def random_forest_like(n_trees: int, depth: int, f: int, seed: int = 78, device=
     feat = torch.randint(0, f, (n_trees, n_nodes), generator=g, dtype=torch.int32)
     base = torch.tensor([{"cont": 8.5, "count": 1.0, "fico": 700.0, "term": 48.0, "onehot": 1.0}[c[1]] for c in cols])
     spread = torch.tensor([{"cont": 2.0, "count": 1.0, "fico": 40.0, "term": 0.0, "onehot": 0.0}[c[1]] for c in cols])
-    thr = base[feat.long()] + spread[feat.long()] * torch.randn((n_trees, n_nodes), generator=g)
+    z = torch.randn((n_trees, n_nodes), generator=g)
+    if grid > 0:
+        z = torch.clamp(torch.round(z * (grid / 3.0)), -grid, grid) / (grid / 3.0)
+    thr = base[feat.long()] + spread[feat.long()] * z
     leafv = 0.05 * torch.randn((n_trees, n_nodes), generator=g)
     cond = torch.where(left >= 0, thr, leafv).to(torch.float32)
     dl = torch.randint(0, 2, (n_trees, n_nodes), generator=g, dtype=torch.uint8)

@@ -166,6 +166,28 @@ int cb_predict_heap(const float* X, int64_t n_rows, int n_features, int64_t ldx,
                     const float* leaf, int n_trees, int depth, float base_margin, float* out_margin,
                     float* out_proba, void* stream);
 
+/* ---- K8 on quantised inputs (the fastest form; same call sites, bit-identical results).  A split "x < thr" only
+ * compares x with one of the forest's own thresholds, so a row is first reduced to one byte per feature
+ * (cb_bin_rows_u8 against the forest's threshold table: per feature its distinct split_cond values ascending, then
+ * +inf; code = number of thresholds <= x, 255 = missing; at most 254 thresholds per feature), and "x < t_k"
+ * becomes "code <= k".
+ * cb_predict_q8_plan: trees per shared-memory chunk and plane_base, the shared-window address the kernel's code
+ * planes start at on this device (it goes into every node word and back into cb_predict_q8, which checks it).
+ * codes: u8 [n_rows][ldc] row major, ldc = 4 * odd >= n_features, 16-byte aligned.
+ * forest: u32 [Tp][2 << depth] per tree in 1-based heap order: word 0 unused, words 1 .. 2^depth - 1 the nodes
+ * = span << 16 | plane_base + (default_left * n_features + feature) * 128 with span = k (+1 when default_left;
+ * pass-through and padding nodes: plane_base), words 2^depth .. 2^(depth+1) - 1 the leaf values (f32 bits).
+ * Tp = n_trees rounded up to whole chunks, 16-byte aligned.  depth <= 10; plane_base + 256 * n_features <= 65536
+ * (about 250 features), else cb_predict_q8_plan reports CB_ERR_UNSUPPORTED and cb_predict_heap is the path.
+ * cb_bin_rows_u8: K2 with the table of a 32-feature slab held in shared memory; natural column order, row major,
+ * same codes as cb_bin_pack_u8 (cuts f32 [n_features][256], n_cuts i32 [n_features]). */
+int cb_predict_q8_plan(int n_features, int depth, int64_t ldc, int* chunk_trees, uint32_t* plane_base);
+int cb_bin_rows_u8(const float* X, int64_t n_rows, int n_features, int64_t ldx, const float* cuts,
+                   const int32_t* n_cuts, uint8_t* codes, int64_t ldc, void* stream);
+int cb_predict_q8(const uint8_t* codes, int64_t n_rows, int n_features, int64_t ldc, const uint32_t* forest,
+                  int n_trees, int depth, float base_margin, uint32_t plane_base, float* out_margin,
+                  float* out_proba, void* stream);
+
 /* ---- fused trainer: one boosting round = K3 + per level (K4, K9, K5, K6) + K7, with every
  * split decision kept on the device (no host synchronisation inside a tree).
  * Replaces the body of XGBClassifier.fit's boosting loop. */

@@ -424,6 +424,88 @@ def test_predict_fixture_forest(ops, fixture_forest):
     assert b.predict_device(_dev(X[:0])).shape == (0,)
 
 
+def _random_forest(rng, n_trees, n_features, max_depth, n_thr):
+    """Random trees in wire format (ragged depth), thresholds from a small per-feature pool so codes collide."""
+    pools = [np.sort(rng.normal(size=rng.integers(1, n_thr + 1)).astype(np.float32)) for _ in range(n_features)]
+    left, right, feat, cond, dl, offs = [], [], [], [], [], [0]
+    for _ in range(n_trees):
+        nodes = []                                   # [left, right, feat, cond, dl]
+
+        def grow(d):
+            i = len(nodes)
+            nodes.append(None)
+            if d == max_depth or (d > 0 and rng.random() < 0.2):
+                nodes[i] = [-1, -1, 0, np.float32(rng.normal() * 0.1), 0]
+                return i
+            j = int(rng.integers(n_features))
+            rec = [0, 0, j, pools[j][rng.integers(len(pools[j]))], int(rng.random() < 0.5)]
+            nodes[i] = rec
+            rec[0] = grow(d + 1)
+            rec[1] = grow(d + 1)
+            return i
+        grow(0)
+        for r in nodes:
+            left.append(r[0]); right.append(r[1]); feat.append(r[2]); cond.append(r[3]); dl.append(r[4])
+        offs.append(len(left))
+    f = {"tree_offsets": np.array(offs, np.int64), "left": np.array(left, np.int32), "right": np.array(right, np.int32),
+         "split_index": np.array(feat, np.int32), "split_cond": np.array(cond, np.float32),
+         "default_left": np.array(dl, np.uint8)}
+    n = len(left)
+    f["parent"] = np.zeros(n, np.int32)
+    for k in ("base_weight", "loss_chg", "sum_hess"):
+        f[k] = np.zeros(n, np.float32)
+    return f, pools
+
+
+@pytest.mark.parametrize("n_rows,n_features,n_trees,depth", [(1, 3, 1, 1), (127, 7, 5, 3), (128, 150, 37, 6), (1000, 250, 19, 6),
+                                                            (4133, 150, 70, 8), (513, 20, 300, 6)])
+def test_predict_quantised_matches_float_kernels(ops, n_rows, n_features, n_trees, depth, monkeypatch):
+    """K8 on quantised inputs (codes against the forest's own thresholds) = the f32 kernels = the oracle, bit for bit:
+    values exactly on, just below and just above thresholds, +-inf, -0.0, NaN with either default direction."""
+    from cobalt_smart_lender_ai_b200.booster import Booster
+    rng = np.random.default_rng(n_rows + n_trees)
+    fo, pools = _random_forest(rng, n_trees, n_features, depth, 40)
+    X = np.zeros((n_rows, n_features), np.float32)
+    for j in range(n_features):
+        base = rng.choice(pools[j], size=n_rows)
+        kind = rng.integers(0, 6, size=n_rows)
+        X[:, j] = np.where(kind == 0, base, np.where(kind == 1, np.nextafter(base, np.float32(-np.inf)),
+                           np.where(kind == 2, np.nextafter(base, np.float32(np.inf)), rng.normal(size=n_rows)))).astype(np.float32)
+    X[rng.random(X.shape) < 0.08] = np.nan
+    X[rng.random(X.shape) < 0.01] = np.inf
+    X[rng.random(X.shape) < 0.01] = -np.inf
+    X[rng.random(X.shape) < 0.01] = -0.0
+    want = O.predict_margin(X, fo["tree_offsets"], fo["left"], fo["right"], fo["split_index"], fo["split_cond"],
+                            fo["default_left"], 0.0)
+    for mode in ("q8", "f32"):
+        monkeypatch.setenv("COBALT_PREDICT", mode)
+        b = Booster(fo, n_features, None, 0.5)
+        got = b.predict_device(_dev(X), output_margin=True).cpu().numpy()
+        assert (b._device_q8(torch.device("cuda")) is not None) == (mode == "q8")
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), mode
+
+
+def test_predict_quantised_falls_back(ops):
+    """More than 254 distinct thresholds on one feature, or too many features for the 16-bit offset field (about
+    250): the f32 kernel scores instead."""
+    from cobalt_smart_lender_ai_b200.booster import Booster
+    rng = np.random.default_rng(9)
+    fo, _ = _random_forest(rng, 400, 2, 6, 4000)
+    X = rng.normal(size=(300, 2)).astype(np.float32)
+    b = Booster(fo, 2, None, 0.5)
+    assert b._device_q8(torch.device("cuda")) is None
+    want = O.predict_margin(X, fo["tree_offsets"], fo["left"], fo["right"], fo["split_index"], fo["split_cond"],
+                            fo["default_left"], 0.0)
+    assert np.array_equal(b.predict_device(_dev(X), output_margin=True).cpu().numpy().view(np.uint32), want.view(np.uint32))
+    fo2, _ = _random_forest(rng, 5, 300, 4, 10)
+    X2 = rng.normal(size=(50, 300)).astype(np.float32)
+    b2 = Booster(fo2, 300, None, 0.5)
+    assert b2._device_q8(torch.device("cuda")) is None
+    want2 = O.predict_margin(X2, fo2["tree_offsets"], fo2["left"], fo2["right"], fo2["split_index"], fo2["split_cond"],
+                             fo2["default_left"], 0.0)
+    assert np.array_equal(b2.predict_device(_dev(X2), output_margin=True).cpu().numpy().view(np.uint32), want2.view(np.uint32))
+
+
 def test_estimator_end_to_end(ops, data):
     """fit/predict_proba/predict/feature_importances_/get_score/pickle through the drop-in class."""
     import pickle
