@@ -442,15 +442,15 @@ int cb_predict_heap(const float* X, int64_t n, int f, int64_t ldx, const uint64_
 // the two tree-chunk buffers take what is left, >= 8 trees each)
 constexpr int kQ8Ilp = 16;                 // trees in flight per thread
 static int q8_chunk_trees(const DeviceInfo& di, int f, int depth, int64_t ldc, int* smem_bytes) {
+  (void)ldc;
   const int64_t TB = (int64_t)8 << depth;
   const int64_t planes = ((int64_t)2 * f * 128 + 127) & ~(int64_t)127;
-  const int64_t staging = (ldc * 128 + 127) & ~(int64_t)127;     // aliases the ring
   const int64_t per_sm = (int64_t)di.smem_optin + 1024;          // opt-in per-CTA limit + its 1 KB reserve = the SM's carve-out
-  for (int k = 4; k >= 1; --k) {
+  for (int k = 5; k >= 1; --k) {                                 // CTAs per SM: the walk is latency bound, warps count
     const int64_t avail = per_sm / k - 1024 - 256 - planes;
     int chunk = (int)std::min<int64_t>(avail / (kQ8Stages * TB), 64) & ~(kQ8Ilp - 1);
-    if (chunk >= kQ8Ilp && (int64_t)kQ8Stages * chunk * TB >= staging) {
-      if (smem_bytes) *smem_bytes = (int)(planes + kQ8Stages * chunk * TB + 8 * (kQ8Stages + 1));
+    if (chunk >= kQ8Ilp) {
+      if (smem_bytes) *smem_bytes = (int)(planes + kQ8Stages * chunk * TB + 8 * kQ8Stages);
       return chunk;
     }
   }

@@ -683,8 +683,8 @@ __global__ void __launch_bounds__(256) predict_heap_kernel(const float* __restri
 // and "x < t_k" becomes "code <= k", bit for bit the same decision.  That makes a node 4 bytes instead
 // of 8 and a feature value 1 byte instead of 4: 2 shared-memory wavefronts per (warp, level) instead of
 // ~3.75, and 2 ALU-pipe instructions instead of 5 (the two resources the f32 kernel is bound by).
-//   codes  : row major [n][ldc] bytes, ldc = 4 * odd: a tile of 128 rows is ONE contiguous block, fetched
-//            with one bulk copy (TMA) and transposed from shared to shared memory without bank conflicts.
+//   codes  : row major [n][ldc] bytes (ldc a multiple of 4), written by K2 a batch at a time and still in L2
+//            when the walk reads them.
 //   tile   : two byte planes [f][128]: plane 0 holds the codes (missing = 255, never <= span), plane 1
 //            holds code + 1 with missing = 0 (always <= span): default-left nodes read plane 1, so the
 //            missing rule costs no instruction.  Row r of a column sits at byte 4 * (r % 32) + r / 32:
@@ -749,7 +749,7 @@ __global__ void smem_base_probe_kernel(uint32_t* out) {
   *out = (uint32_t)__cvta_generic_to_shared(probe_s);
 }
 
-constexpr int kQ8Stages = 4;               // tree-chunk buffers in flight: a chunk is walked faster than a bulk copy lands
+constexpr int kQ8Stages = 2;               // tree-chunk buffers: one being walked, one in flight
 // one level of one tree walk.  a = shared address of the node; children of the node at S + 4i are at
 // 2 * (S + 4i) - S (+ 4): cl = -S, cr = 4 - S.  The shift and both address updates run on the FMA pipe; the ALU
 // pipe (half rate) only sees the offset mask/or and the compare.
@@ -764,12 +764,11 @@ __device__ __forceinline__ void q8_step(uint32_t& a, uint32_t x, uint32_t q, uin
 }
 
 template <int ILP, int DEPTH>
-__global__ void __launch_bounds__(128) predict_q8_kernel(const uint8_t* __restrict__ codes, int64_t n, int f, int64_t ldc,
+__global__ void __launch_bounds__(128, 4) predict_q8_kernel(const uint8_t* __restrict__ codes, int64_t n, int f, int64_t ldc,
                                                          const uint32_t* __restrict__ forest, int n_trees,
                                                          int chunk_trees, float base_margin, uint32_t plane_base,
                                                          float* __restrict__ out_margin, float* __restrict__ out_proba) {
-  // planes [2][f][128] | ring of kQ8Stages tree-chunk buffers | mbarriers.  The row-major staging copy of the tile
-  // ([128][ldc]) lives in the ring too and is dead before the first chunk is requested.  No static shared memory:
+  // planes [2][f][128] | kQ8Stages tree-chunk buffers | mbarriers.  No static shared memory:
   // the planes start at the bottom of the CTA's shared window, whose address (plane_base, cb_predict_q8_plan) is
   // already added to every node's offset field, so "(node & 0xFFFF) | row byte" IS the shared address of the code.
   extern __shared__ __align__(128) uint8_t q8s[];
@@ -779,16 +778,14 @@ __global__ void __launch_bounds__(128) predict_q8_kernel(const uint8_t* __restri
   constexpr uint32_t TB = 8u << DEPTH;              // bytes per tree
   const uint32_t plane_b = (uint32_t)f * R;
   uint8_t* buf0 = q8s + ((2 * plane_b + 127) & ~127u);
-  uint8_t* stage = buf0;
   const uint32_t buf_b = (uint32_t)chunk_trees * TB;
   uint64_t* bars = reinterpret_cast<uint64_t*>(buf0 + (size_t)kQ8Stages * buf_b);
   const int n_chunks = (n_trees + chunk_trees - 1) / chunk_trees;   // the array is padded to whole chunks
   const int64_t row0 = (int64_t)blockIdx.x * R;
   const int nrow = (int)min((int64_t)R, n - row0);
-  const bool bulk_tile = nrow == R;                 // a partial last tile is copied by hand (size not a multiple of 16)
   if (threadIdx.x == 0) {
 #pragma unroll
-    for (int k = 0; k <= kQ8Stages; ++k) mbar_init(&bars[k], 1);
+    for (int k = 0; k < kQ8Stages; ++k) mbar_init(&bars[k], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -797,40 +794,35 @@ __global__ void __launch_bounds__(128) predict_q8_kernel(const uint8_t* __restri
     mbar_expect_tx(bar, buf_b);
     bulk_g2s(buf0 + (size_t)(c % kQ8Stages) * buf_b, reinterpret_cast<const uint8_t*>(forest) + (size_t)c * buf_b, buf_b, bar);
   };
-  if (threadIdx.x == 0 && bulk_tile) {
-    mbar_expect_tx(&bars[kQ8Stages], (uint32_t)ldc * R);
-    bulk_g2s(stage, codes + row0 * ldc, (uint32_t)ldc * R, &bars[kQ8Stages]);
+  if (threadIdx.x == 0) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    for (int c = 0; c < kQ8Stages && c < n_chunks; ++c) issue(c);   // the first chunks travel while the tile is filled
   }
   const uint32_t r = threadIdx.x;
   const uint32_t pr = 4u * (r & 31u) + (r >> 5);     // this row's byte inside a feature column
-  if (bulk_tile) {
-    mbar_wait(&bars[kQ8Stages], 0u);
-  } else {
-    const int wpr = (int)(ldc >> 2);
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(codes + row0 * ldc);
-    for (int i = threadIdx.x; i < nrow * wpr; i += R) reinterpret_cast<uint32_t*>(stage)[i] = __ldg(src + i);
-    __syncthreads();
-  }
-  if ((int)r < nrow) {                               // transpose: lane = row; ldc / 4 is odd, so the word reads spread over the banks
-    const uint32_t* mine = reinterpret_cast<const uint32_t*>(stage + (size_t)r * ldc);
-    for (int w = 0; 4 * w < f; ++w) {
-      const uint32_t v = mine[w];
+  if ((int)r < nrow) {
+    // tile fill straight from global memory, lane = row: a warp load touches 32 rows x 4 bytes (32 sectors), and
+    // the next 7 loads of the warp hit the same sectors in L1; the byte stores go to 32 different banks
+    const uint32_t* mine = reinterpret_cast<const uint32_t*>(codes + (row0 + r) * ldc);
+    for (int w0 = 0; 4 * w0 < f; w0 += 8) {
+      uint32_t v[8];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int c = 4 * w + j;
-        if (c < f) {
-          const uint32_t b = (v >> (8 * j)) & 255u;
-          q8s[(uint32_t)c * R + pr] = (uint8_t)b;
-          q8s[plane_b + (uint32_t)c * R + pr] = (uint8_t)(b + 1u);   // 255 (missing) wraps to 0
+      for (int u = 0; u < 8; ++u) v[u] = (4 * (w0 + u) < f) ? __ldg(mine + w0 + u) : 0u;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int c = 4 * (w0 + u) + j;
+          if (c < f) {
+            const uint32_t bb = (v[u] >> (8 * j)) & 255u;
+            q8s[(uint32_t)c * R + pr] = (uint8_t)bb;
+            q8s[plane_b + (uint32_t)c * R + pr] = (uint8_t)(bb + 1u);   // 255 (missing) wraps to 0
+          }
         }
       }
     }
   }
-  __syncthreads();                                   // planes complete, staging dead: the ring may fill
-  if (threadIdx.x == 0) {
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    for (int c = 0; c < kQ8Stages && c < n_chunks; ++c) issue(c);
-  }
+  __syncthreads();                                   // planes complete
   float m = base_margin;
   for (int c = 0; c < n_chunks; ++c) {
     const uint8_t* buf = buf0 + (size_t)(c % kQ8Stages) * buf_b;
