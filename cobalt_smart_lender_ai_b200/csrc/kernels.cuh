@@ -175,7 +175,7 @@ __device__ inline void plan_ctas(HistPlan* plan, int n_build, const int* begins,
   int spare = grid - n_build, b = 0, p = 0;
   for (int j = 0; j < n_build; ++j) {
     int nj = 1 + (total > 0 ? (int)((long long)spare * counts[j] / total) : 0);
-    int need = (counts[j] + 1023) / 1024;                   // at least 1024 rows per CTA
+    int need = (counts[j] + 255) / 256;                     // at least 256 rows per CTA (2 warp iterations per column block)
     nj = max(1, min(nj, need));
     int per = (counts[j] + nj - 1) / nj;
     per = (per + 31) & ~31;
