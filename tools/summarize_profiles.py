@@ -35,6 +35,8 @@ def launches(path, tag):
         v = v / 1e3 if r["Metric Unit"] == "ns" else (v * 1e3 if r["Metric Unit"] == "ms" else v)
         seq.append((name, v))
     starts = [i for i, (n, _) in enumerate(seq) if n.startswith("grad_kernel")]
+    if len(starts) < 2:
+        raise SystemExit(f"{path}: need at least two boosting rounds in the launch list, found {len(starts)}")
     a, b = (starts[3], starts[4]) if len(starts) > 4 else (starts[-2], starts[-1])
     agg = collections.OrderedDict()
     for n, v in seq[a:b]:
@@ -57,7 +59,7 @@ def launches(path, tag):
         w.writerow([])
         w.writerow(["# one-off preparation (sketch, binning) and scoring launches"])
         pre = collections.OrderedDict()
-        for n, v in seq[:starts[0]] + [x for x in seq[starts[-1]:] if "predict" in x[0]]:
+        for n, v in seq[:starts[0]] + [x for x in seq[starts[-1]:] if "predict" in x[0] or "bin_rows" in x[0]]:
             c = pre.setdefault(n, [0, 0.0])
             c[0] += 1
             c[1] += v
