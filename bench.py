@@ -261,6 +261,7 @@ def run_ours(args):
         del bp_
     cuts_cpu, nc_cpu, mv_cpu = cuts.cpu().numpy(), n_cuts.cpu().numpy(), min_vals.cpu().numpy()
     y_cpu = y.cpu().numpy()
+    peer_mode = bool(tr.peer_mode)
     tr.close()
     del tr, bins, bins_cm
 
@@ -368,7 +369,7 @@ def run_ours(args):
                                                 "binned shard may fit L2 at N>=4 (strong scaling of a 352 MB matrix)",
                                                 "parallelism": (f"rows sharded x{world}, " + (
                                                     "per-level histograms summed over NVLink peer memory inside the split scan"
-                                                    if tr.peer_mode else "NCCL allreduce of per-level histograms"))
+                                                    if peer_mode else "NCCL allreduce of per-level histograms"))
                                                 if world > 1 else "single GPU"},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clk.summary(), "scoring": scoring, "prep_ms": round(t_prep, 2), "train_auc_200k": auc}
