@@ -100,6 +100,9 @@ _SIGS = {
     "cb_predict": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _I, _F, _VP, _VP, _VP]),
     "cb_predict_heap_plan": (C.c_int, [_I, _I, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "cb_predict_heap": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _I, _I, _F, _VP, _VP, _VP]),
+    "cb_tree_shap_workspace_bytes": (C.c_int, [_I64, _I, _I, _I64, C.POINTER(C.c_size_t)]),
+    "cb_tree_shap": (C.c_int, [_VP, _I64, _I, _I64, _VP, _I, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _F, _I, _VP, _VP,
+                               C.c_size_t, _VP]),
     "cb_predict_q8_plan": (C.c_int, [_I, _I, _I64, C.POINTER(C.c_int), C.POINTER(C.c_uint32)]),
     "cb_bin_rows_u8": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _VP, _I64, _VP]),
     "cb_predict_q8": (C.c_int, [_VP, _I64, _I, _I64, _VP, _I, _I, _F, C.c_uint32, _VP, _VP, _VP]),

@@ -2,8 +2,8 @@
 
 Same module-level names (``app``, ``xgb_model``, ``SingleInput``, ``BulkInput``, ``predict_proba_df``), same three
 routes and JSON shapes (reference :96-108, :113-126, :128-143).  Differences, all outside the hot path:
-the model comes from a local file (``COBALT_MODEL_PATH``) instead of S3 (:36-54), and SHAP values are not
-computed (TreeSHAP is a separate algorithm): ``shap_values`` / ``base_value`` are ``None``.
+the model comes from a local file (``COBALT_MODEL_PATH``) instead of S3 (:36-54), and ``shap.TreeExplainer`` is this
+package's ``explain.TreeExplainer`` (path-dependent TreeSHAP on the GPU).
 The model file may be a pickle of this package's XGBClassifier or the reference's own xgboost pickle / ``.ubj``
 (decoded without xgboost, see ``ubjson.py``).
 """
@@ -20,11 +20,13 @@ import pandas as pd
 from fastapi import FastAPI, File, HTTPException, UploadFile
 from pydantic import BaseModel, ConfigDict, Field
 
+from ..explain import TreeExplainer
+
 local_model_path = Path(os.environ.get("COBALT_MODEL_PATH", "models/xgb_model_tree.pkl"))
 
 app = FastAPI(title="Cobalt XGBoost Inference API")
 xgb_model = None
-explainer = None   # kept for interface parity; TreeSHAP is out of scope here
+explainer = None
 
 
 def load_model(path) -> object:
@@ -43,11 +45,12 @@ def load_model(path) -> object:
 
 @asynccontextmanager
 async def lifespan(app: FastAPI):
-    global xgb_model
+    global xgb_model, explainer
     try:
         print(f"[INFO] Loading model from {local_model_path}")
         xgb_model = load_model(local_model_path)
-        print("[INFO] Model ready.")
+        explainer = TreeExplainer(xgb_model)               # reference :46: shap.TreeExplainer(xgb_model)
+        print("[INFO] Model and SHAP Explainer ready.")
     except Exception as e:
         print(f"[ERROR] Model load failed: {e}")
         raise RuntimeError("Failed to load model.")
@@ -93,10 +96,11 @@ def predict_proba_df(df: pd.DataFrame) -> np.ndarray:
 def predict_single(input_data: SingleInput):
     row = pd.DataFrame([input_data.model_dump(by_alias=True)])
     y_proba = predict_proba_df(row)[0]
+    shap_vals = explainer.shap_values(row)[0].tolist()
     return {
         "prob_default": float(y_proba),
-        "shap_values": None,
-        "base_value": None,
+        "shap_values": shap_vals,
+        "base_value": float(explainer.expected_value),
         "features": row.columns.tolist(),
         "input_row": row.iloc[0].to_dict(),
     }

@@ -205,6 +205,41 @@ class Booster:
                                want_proba=not output_margin)
         return m if output_margin else p
 
+    def max_depth(self) -> int:
+        """Depth of the deepest tree; also checks that children carry larger ids than their parent."""
+        fo = self.forest
+        offs = fo["tree_offsets"]
+        left, right = np.asarray(fo["left"], np.int64), np.asarray(fo["right"], np.int64)
+        depth = np.zeros(len(left), np.int32)
+        best = 0
+        for t in range(len(offs) - 1):
+            o, e = int(offs[t]), int(offs[t + 1])
+            for i in range(o, e):
+                if left[i] >= 0:
+                    if left[i] <= i - o or right[i] <= i - o:
+                        raise ValueError("forest numbering: a child id does not follow its parent")
+                    depth[o + left[i]] = depth[o + right[i]] = depth[i] + 1
+                    best = max(best, int(depth[i]) + 1)
+        return best
+
+    def predict_contribs_device(self, X: torch.Tensor) -> torch.Tensor:
+        """Path-dependent TreeSHAP on the GPU (what xgboost's pred_contribs / shap.TreeExplainer return):
+        CUDA f32 [n, n_features + 1], last column = expected value; rows sum to the margin."""
+        if X.shape[1] != self.n_features:
+            raise ValueError(f"Feature shape mismatch, expected: {self.n_features}, got {X.shape[1]}")
+        key = "shap:" + str(X.device)
+        if key not in self._dev_cache:
+            fo = self.forest
+            if "sum_hess" not in fo:
+                raise ValueError("TreeSHAP needs the node covers (sum_hess)")
+            dt = {"tree_offsets": np.int64, "left": np.int32, "right": np.int32, "split_index": np.int32,
+                  "split_cond": np.float32, "default_left": np.uint8, "sum_hess": np.float32}
+            with torch.cuda.device(X.device):
+                dev = {k: torch.from_numpy(np.ascontiguousarray(fo[k], d)).to(X.device) for k, d in dt.items()}
+            self._dev_cache[key] = (dev, self.max_depth())
+        dev, depth = self._dev_cache[key]
+        return ops.tree_shap(X, dev, base_margin_of(self.base_score), depth)
+
     def _device_q8(self, device):
         """Quantised-input form of the forest (the fastest scorer), or None when it does not apply."""
         key = "q8:" + str(device)

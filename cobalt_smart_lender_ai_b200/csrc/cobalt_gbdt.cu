@@ -6,6 +6,7 @@
 #include "sketch.cuh"
 #include "hist_cf.cuh"
 #include "trainer.cuh"
+#include "shap.cuh"
 
 namespace cb {
 thread_local char g_err[512] = "";
@@ -541,6 +542,45 @@ int cb_predict_q8(const uint8_t* codes, int64_t n, int f, int64_t ldc, const uin
     case 9: return launch(predict_q8_kernel<kQ8Ilp, 9>);
     default: return launch(predict_q8_kernel<kQ8Ilp, 10>);
   }
+}
+
+// ---------------------------------------------------------------------------- K10 TreeSHAP
+int cb_tree_shap_workspace_bytes(int64_t n_rows, int n_features, int n_trees, int64_t n_nodes, size_t* bytes) {
+  if (!bytes || n_rows < 0 || n_features <= 0 || n_trees < 0 || n_nodes < 0) return fail(CB_ERR_INVALID, "cb_tree_shap_workspace_bytes: bad arguments");
+  Bump b(nullptr);
+  b.take<float>((size_t)n_rows * n_trees * (n_features + 1));
+  b.take<float>((size_t)n_nodes);
+  b.take<float>((size_t)n_trees);
+  *bytes = b.used();
+  return CB_OK;
+}
+
+int cb_tree_shap(const float* X, int64_t n, int f, int64_t ldx, const int64_t* tree_off, int n_trees, int64_t n_nodes,
+                 const int32_t* left, const int32_t* right, const int32_t* split_index, const float* split_cond,
+                 const uint8_t* default_left, const float* sum_hess, float base_margin, int max_depth, float* out,
+                 void* workspace, size_t workspace_bytes, void* stream) {
+  if (n == 0) return CB_OK;
+  if (!X || !tree_off || !left || !right || !split_index || !split_cond || !default_left || !sum_hess || !out || !workspace ||
+      n < 0 || f <= 0 || ldx < f || n_trees < 0 || n_nodes < 0)
+    return fail(CB_ERR_INVALID, "cb_tree_shap: bad arguments");
+  if (max_depth > kShapMaxDepth) return fail(CB_ERR_UNSUPPORTED, "cb_tree_shap: trees deeper than %d levels", kShapMaxDepth);
+  size_t need = 0;
+  cb_tree_shap_workspace_bytes(n, f, n_trees, n_nodes, &need);
+  if (workspace_bytes < need) return fail(CB_ERR_WORKSPACE, "cb_tree_shap: workspace %zu < %zu bytes", workspace_bytes, need);
+  cudaStream_t s = (cudaStream_t)stream;
+  Bump b(workspace);
+  float* ws = b.take<float>((size_t)n * n_trees * (f + 1));
+  float* node_mean = b.take<float>((size_t)n_nodes);
+  float* tree_mean = b.take<float>((size_t)n_trees);
+  ShapForest fo{tree_off, left, right, split_index, split_cond, default_left, sum_hess};
+  CB_CUDA(cudaMemsetAsync(ws, 0, sizeof(float) * (size_t)n * n_trees * (f + 1), s));
+  if (n_trees > 0) {
+    shap_means_kernel<<<ceil_div(n_trees, 128), 128, 0, s>>>(fo, n_trees, node_mean, tree_mean);
+    shap_trees_kernel<<<(unsigned)ceil_div(n * n_trees, (int64_t)128), 128, 0, s>>>(X, n, f, ldx, fo, n_trees, ws);
+  }
+  shap_sum_kernel<<<(unsigned)ceil_div(n * (f + 1), (int64_t)256), 256, 0, s>>>(ws, tree_mean, n, f, n_trees, base_margin, out);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
 }
 
 // ---------------------------------------------------------------------------- trainer

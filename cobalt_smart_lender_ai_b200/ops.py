@@ -263,3 +263,28 @@ def predict_q8(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, forest
                                 int(plane_base), _ptr(m[r0:r1]) if m is not None else None,
                                 _ptr(p[r0:r1]) if p is not None else None, _stream()))
     return m, p
+
+
+def tree_shap(X: torch.Tensor, forest: dict, base_margin: float, max_depth: int, batch_rows: int | None = None) -> torch.Tensor:
+    """K10.  forest: dict of CUDA tensors tree_offsets i64, left/right/split_index i32, split_cond f32,
+    default_left u8, sum_hess f32.  Returns f32 [n, f + 1] (last column: expected value incl. base_margin)."""
+    _need_cuda(X, *forest.values())
+    assert X.dtype == torch.float32 and X.stride(1) == 1
+    n, f = X.shape
+    T = forest["tree_offsets"].numel() - 1
+    n_nodes = forest["left"].numel()
+    lib = _lib.load()
+    if batch_rows is None:                               # keep the per-(row, tree) slices under ~256 MB
+        batch_rows = max(1, (1 << 26) // max(1, T * (f + 1)))
+    out = torch.empty((n, f + 1), dtype=torch.float32, device=X.device)
+    need = C.c_size_t()
+    check(lib.cb_tree_shap_workspace_bytes(min(n, batch_rows), f, T, n_nodes, C.byref(need)))
+    ws = workspace(need.value, X.device)
+    wp, wb = _aligned(ws)
+    for r0 in range(0, n, batch_rows):
+        r1 = min(n, r0 + batch_rows)
+        check(lib.cb_tree_shap(_ptr(X[r0:r1]), r1 - r0, f, _ld(X), _ptr(forest["tree_offsets"]), T, n_nodes,
+                               _ptr(forest["left"]), _ptr(forest["right"]), _ptr(forest["split_index"]),
+                               _ptr(forest["split_cond"]), _ptr(forest["default_left"]), _ptr(forest["sum_hess"]),
+                               float(base_margin), int(max_depth), _ptr(out[r0:r1]), wp, wb, _stream()))
+    return out

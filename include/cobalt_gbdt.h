@@ -188,6 +188,20 @@ int cb_predict_q8(const uint8_t* codes, int64_t n_rows, int n_features, int64_t 
                   int n_trees, int depth, float base_margin, uint32_t plane_base, float* out_margin,
                   float* out_proba, void* stream);
 
+/* ---- K10 path-dependent TreeSHAP (Lundberg, Erion & Lee 2018, Algorithm 2).  Replaces
+ * shap.TreeExplainer(xgb_model).shap_values(row) / .expected_value (src/api/cobalt_fast_api.py:46, :100-105).
+ * Forest in the wire format: arrays concatenated over trees, tree_off i64 [n_trees + 1], child ids
+ * relative to the tree start and larger than the parent's, left == -1 marks a leaf whose value is split_cond;
+ * sum_hess is the node cover.  max_depth: depth of the deepest tree (<= 12, computed by the host).
+ * out: f32 [n_rows][n_features + 1]; the last column is the expected value (cover-weighted mean of the leaves of
+ * every tree, plus base_margin); every row of out sums to the row's margin.  f32 arithmetic in a fixed order:
+ * bit-identical to the oracle's R13. */
+int cb_tree_shap_workspace_bytes(int64_t n_rows, int n_features, int n_trees, int64_t n_nodes, size_t* bytes);
+int cb_tree_shap(const float* X, int64_t n_rows, int n_features, int64_t ldx, const int64_t* tree_off, int n_trees,
+                 int64_t n_nodes, const int32_t* left, const int32_t* right, const int32_t* split_index,
+                 const float* split_cond, const uint8_t* default_left, const float* sum_hess, float base_margin,
+                 int max_depth, float* out, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- fused trainer: one boosting round = K3 + per level (K4, K9, K5, K6) + K7, with every
  * split decision kept on the device (no host synchronisation inside a tree).
  * Replaces the body of XGBClassifier.fit's boosting loop. */

@@ -482,3 +482,147 @@ int orc_predict_margin(const float* X, int64_t n, int f, int64_t ldx, const int6
   }
   return 0;
 }
+
+/* ------------------------------------------------------------- R13: TreeSHAP (8f-3) ---
+ * Path-dependent TreeSHAP, Lundberg, Erion & Lee 2018 ("Consistent individualized feature
+ * attribution for tree ensembles", Algorithm 2): what shap.TreeExplainer(xgb_model).shap_values(row)
+ * returns for an xgboost model (src/api/cobalt_fast_api.py:46, :100-105; shap hands xgboost models to
+ * xgboost's pred_contribs, xgboost-3.0.0 src/predictor, un-vendored).  Node cover = sum_hess.
+ * Per tree the contributions go to a zeroed phi_t[f+1] (slot f = the tree's expected value, the
+ * cover-weighted mean of its leaves); the forest's phi is the sum of the phi_t in tree order, plus
+ * base_margin in slot f.  All arithmetic is f32, one rounding per operation, in the order written
+ * here (the CUDA kernel repeats it instruction for instruction).
+ * PARITY PIN STATUS: "parity unpinned" against shap/xgboost (neither is installable here); pinned
+ * instead to the DEFINITION: tests/test_oracle_golden.py enumerates all feature subsets of small
+ * forests (Shapley value of the path-dependent conditional expectation, f64) and compares. */
+#define ORC_SHAP_MAXD 12
+typedef struct { int feat; float zero, one, pw; } orc_path_t;
+
+static void shap_extend(orc_path_t* p, int ud, float zero, float one, int feat) {
+  p[ud].feat = feat; p[ud].zero = zero; p[ud].one = one; p[ud].pw = ud == 0 ? 1.0f : 0.0f;
+  for (int i = ud - 1; i >= 0; --i) {
+    p[i + 1].pw += one * p[i].pw * (float)(i + 1) / (float)(ud + 1);
+    p[i].pw = zero * p[i].pw * (float)(ud - i) / (float)(ud + 1);
+  }
+}
+static void shap_unwind(orc_path_t* p, int ud, int k) {
+  const float one = p[k].one, zero = p[k].zero;
+  float next = p[ud].pw;
+  for (int i = ud - 1; i >= 0; --i) {
+    if (one != 0.0f) {
+      const float tmp = p[i].pw;
+      p[i].pw = next * (float)(ud + 1) / ((float)(i + 1) * one);
+      next = tmp - p[i].pw * zero * (float)(ud - i) / (float)(ud + 1);
+    } else {
+      p[i].pw = p[i].pw * (float)(ud + 1) / (zero * (float)(ud - i));
+    }
+  }
+  for (int i = k; i < ud; ++i) { p[i].feat = p[i + 1].feat; p[i].zero = p[i + 1].zero; p[i].one = p[i + 1].one; }
+}
+static float shap_unwound_sum(const orc_path_t* p, int ud, int k) {
+  const float one = p[k].one, zero = p[k].zero;
+  float next = p[ud].pw, total = 0.0f;
+  for (int i = ud - 1; i >= 0; --i) {
+    if (one != 0.0f) {
+      const float tmp = next * (float)(ud + 1) / ((float)(i + 1) * one);
+      total += tmp;
+      next = p[i].pw - tmp * zero * ((float)(ud - i) / (float)(ud + 1));
+    } else {
+      total += p[i].pw / zero / ((float)(ud - i) / (float)(ud + 1));
+    }
+  }
+  return total;
+}
+/* cover-weighted mean of the leaves below `nid` (post-order, f32) */
+static float shap_mean(int64_t o, int nid, const int32_t* left, const int32_t* right, const float* cond,
+                       const float* cover) {
+  if (left[o + nid] == -1) return cond[o + nid];
+  const int l = left[o + nid], r = right[o + nid];
+  const float ml = shap_mean(o, l, left, right, cond, cover), mr = shap_mean(o, r, left, right, cond, cover);
+  return (ml * cover[o + l] + mr * cover[o + r]) / cover[o + nid];
+}
+typedef struct { int nid, ud, poff, feat; float zero, one; } orc_frame_t;
+
+/* phi_t[f+1] of one tree for one row; explicit stack, hot child first (as the recursion would) */
+static void shap_tree(const float* x, int f, int64_t o, const int32_t* left, const int32_t* right,
+                      const int32_t* split_index, const float* cond, const uint8_t* default_left,
+                      const float* cover, float* phi) {
+  orc_path_t path[(ORC_SHAP_MAXD + 2) * (ORC_SHAP_MAXD + 3) / 2];
+  orc_frame_t st[2 * ORC_SHAP_MAXD + 4];
+  int sp = 0;
+  st[sp++] = (orc_frame_t){0, 0, 0, -1, 1.0f, 1.0f};
+  while (sp > 0) {
+    const orc_frame_t fr = st[--sp];
+    orc_path_t* p = path + fr.poff + fr.ud + (fr.ud > 0);   /* own buffer: right behind the parent's ud+1 elements */
+    if (fr.ud > 0) memcpy(p, path + fr.poff, sizeof(orc_path_t) * (size_t)fr.ud);
+    int ud = fr.ud;
+    shap_extend(p, ud, fr.zero, fr.one, fr.feat);
+    const int nid = fr.nid;
+    if (left[o + nid] == -1) {
+      for (int i = 1; i <= ud; ++i) {
+        const float w = shap_unwound_sum(p, ud, i);
+        phi[p[i].feat] += w * (p[i].one - p[i].zero) * cond[o + nid];
+      }
+      continue;
+    }
+    const int sf = split_index[o + nid];
+    const float v = x[sf];
+    const int go_left = (v != v) ? default_left[o + nid] : (v < cond[o + nid]);
+    const int hot = go_left ? left[o + nid] : right[o + nid];
+    const int cold = go_left ? right[o + nid] : left[o + nid];
+    const float w = cover[o + nid];
+    const float hot_zero = cover[o + hot] / w, cold_zero = cover[o + cold] / w;
+    float in_zero = 1.0f, in_one = 1.0f;
+    int k = 0;
+    for (; k <= ud; ++k) if (p[k].feat == sf) break;
+    if (k != ud + 1) {
+      in_zero = p[k].zero; in_one = p[k].one;
+      shap_unwind(p, ud, k);
+      ud -= 1;
+    }
+    const int poff = (int)(p - path);
+    st[sp++] = (orc_frame_t){cold, ud + 1, poff, sf, cold_zero * in_zero, 0.0f};
+    st[sp++] = (orc_frame_t){hot, ud + 1, poff, sf, hot_zero * in_zero, in_one};
+  }
+  (void)f;
+}
+
+/* out: [n][f+1] (last column = expected value incl. base_margin); returns -1 if a tree is deeper than ORC_SHAP_MAXD */
+int orc_tree_shap(const float* X, int64_t n, int f, int64_t ldx, const int64_t* tree_off, int n_trees,
+                  const int32_t* left, const int32_t* right, const int32_t* split_index,
+                  const float* split_cond, const uint8_t* default_left, const float* sum_hess,
+                  float base_margin, float* out) {
+  for (int t = 0; t < n_trees; ++t) {            /* depth check: child ids are larger than the parent's */
+    const int64_t o = tree_off[t], cnt = tree_off[t + 1] - o;
+    int* depth = (int*)calloc((size_t)cnt, sizeof(int));
+    int bad = 0;
+    for (int64_t i = 0; i < cnt; ++i)
+      if (left[o + i] != -1) {
+        depth[left[o + i]] = depth[i] + 1; depth[right[o + i]] = depth[i] + 1;
+        if (depth[i] + 1 > ORC_SHAP_MAXD) bad = 1;
+      }
+    free(depth);
+    if (bad) return -1;
+  }
+  float* means = (float*)malloc(sizeof(float) * (size_t)(n_trees > 0 ? n_trees : 1));
+  for (int t = 0; t < n_trees; ++t) means[t] = shap_mean(tree_off[t], 0, left, right, split_cond, sum_hess);
+#pragma omp parallel
+  {
+    float* phi_t = (float*)malloc(sizeof(float) * (size_t)(f + 1));
+#pragma omp for schedule(static)
+    for (int64_t r = 0; r < n; ++r) {
+      float* phi = out + r * (f + 1);
+      for (int j = 0; j <= f; ++j) phi[j] = 0.0f;
+      for (int t = 0; t < n_trees; ++t) {
+        for (int j = 0; j <= f; ++j) phi_t[j] = 0.0f;
+        shap_tree(X + r * ldx, f, tree_off[t], left, right, split_index, split_cond, default_left, sum_hess, phi_t);
+        phi_t[f] = means[t];
+        for (int j = 0; j <= f; ++j) phi[j] += phi_t[j];
+      }
+      phi[f] += base_margin;
+    }
+    free(phi_t);
+  }
+  free(means);
+  return 0;
+}

@@ -247,6 +247,61 @@ def flatten_forest(fo: dict) -> dict:
     return out
 
 
+def tree_shap(X, tree_offsets, left, right, split_index, split_cond, default_left, sum_hess, base_margin=0.0):
+    """R13: path-dependent TreeSHAP.  Returns f32 [n, f+1]; the last column is the expected value (incl. base_margin)."""
+    X = np.ascontiguousarray(X, np.float32)
+    n, f = X.shape
+    out = np.empty((n, f + 1), np.float32)
+    rc = lib().orc_tree_shap(_p(X), C.c_int64(n), C.c_int(f), C.c_int64(f),
+                             _p(np.ascontiguousarray(tree_offsets, np.int64)), C.c_int(len(tree_offsets) - 1),
+                             _p(np.ascontiguousarray(left, np.int32)), _p(np.ascontiguousarray(right, np.int32)),
+                             _p(np.ascontiguousarray(split_index, np.int32)),
+                             _p(np.ascontiguousarray(split_cond, np.float32)),
+                             _p(np.ascontiguousarray(default_left, np.uint8)),
+                             _p(np.ascontiguousarray(sum_hess, np.float32)), C.c_float(base_margin), _p(out))
+    if rc != 0:
+        raise ValueError("tree_shap: a tree is deeper than 12 levels")
+    return out
+
+
+def shapley_brute_force(x, tree_offsets, left, right, split_index, split_cond, default_left, sum_hess):
+    """The DEFINITION TreeSHAP computes, by enumeration (f64; small forests only): Shapley values of
+    v(S) = E[f(x) | x_S], the expectation taken down the tree with cover-weighted branches for features not in S.
+    Returns (phi [f], expected value)."""
+    import itertools
+    import math
+    x = np.asarray(x, np.float64)
+    f = len(x)
+    phi = np.zeros(f)
+    base = 0.0
+    for t in range(len(tree_offsets) - 1):
+        o = int(tree_offsets[t])
+
+        def ev(nid, S):
+            if left[o + nid] == -1:
+                return float(split_cond[o + nid])
+            j = int(split_index[o + nid])
+            l, r = int(left[o + nid]), int(right[o + nid])
+            if j in S:
+                v = x[j]
+                go_left = bool(default_left[o + nid]) if np.isnan(v) else bool(np.float32(v) < split_cond[o + nid])
+                return ev(l if go_left else r, S)
+            cl, cr = float(sum_hess[o + l]), float(sum_hess[o + r])
+            return (ev(l, S) * cl + ev(r, S) * cr) / (cl + cr)
+        cnt = int(tree_offsets[t + 1]) - o
+        used = sorted({int(split_index[o + i]) for i in range(cnt) if left[o + i] != -1})
+        m = len(used)
+        base += ev(0, frozenset())
+        for i in used:
+            rest = [u for u in used if u != i]
+            for k in range(m):
+                wgt = math.factorial(k) * math.factorial(m - k - 1) / math.factorial(m)
+                for S in itertools.combinations(rest, k):
+                    S = frozenset(S)
+                    phi[i] += wgt * (ev(0, S | {i}) - ev(0, S))
+    return phi, base
+
+
 def predict_margin(X, tree_offsets, left, right, split_index, split_cond, default_left, base_margin=0.0):
     X = np.ascontiguousarray(X, np.float32)
     n, f = X.shape

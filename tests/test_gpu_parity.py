@@ -424,37 +424,7 @@ def test_predict_fixture_forest(ops, fixture_forest):
     assert b.predict_device(_dev(X[:0])).shape == (0,)
 
 
-def _random_forest(rng, n_trees, n_features, max_depth, n_thr):
-    """Random trees in wire format (ragged depth), thresholds from a small per-feature pool so codes collide."""
-    pools = [np.sort(rng.normal(size=rng.integers(1, n_thr + 1)).astype(np.float32)) for _ in range(n_features)]
-    left, right, feat, cond, dl, offs = [], [], [], [], [], [0]
-    for _ in range(n_trees):
-        nodes = []                                   # [left, right, feat, cond, dl]
-
-        def grow(d):
-            i = len(nodes)
-            nodes.append(None)
-            if d == max_depth or (d > 0 and rng.random() < 0.2):
-                nodes[i] = [-1, -1, 0, np.float32(rng.normal() * 0.1), 0]
-                return i
-            j = int(rng.integers(n_features))
-            rec = [0, 0, j, pools[j][rng.integers(len(pools[j]))], int(rng.random() < 0.5)]
-            nodes[i] = rec
-            rec[0] = grow(d + 1)
-            rec[1] = grow(d + 1)
-            return i
-        grow(0)
-        for r in nodes:
-            left.append(r[0]); right.append(r[1]); feat.append(r[2]); cond.append(r[3]); dl.append(r[4])
-        offs.append(len(left))
-    f = {"tree_offsets": np.array(offs, np.int64), "left": np.array(left, np.int32), "right": np.array(right, np.int32),
-         "split_index": np.array(feat, np.int32), "split_cond": np.array(cond, np.float32),
-         "default_left": np.array(dl, np.uint8)}
-    n = len(left)
-    f["parent"] = np.zeros(n, np.int32)
-    for k in ("base_weight", "loss_chg", "sum_hess"):
-        f[k] = np.zeros(n, np.float32)
-    return f, pools
+from _forests import random_forest as _random_forest  # noqa: E402
 
 
 @pytest.mark.parametrize("n_rows,n_features,n_trees,depth", [(1, 3, 1, 1), (127, 7, 5, 3), (128, 150, 37, 6), (1000, 250, 19, 6),
@@ -504,6 +474,45 @@ def test_predict_quantised_falls_back(ops):
     want2 = O.predict_margin(X2, fo2["tree_offsets"], fo2["left"], fo2["right"], fo2["split_index"], fo2["split_cond"],
                              fo2["default_left"], 0.0)
     assert np.array_equal(b2.predict_device(_dev(X2), output_margin=True).cpu().numpy().view(np.uint32), want2.view(np.uint32))
+
+
+@pytest.mark.parametrize("n_rows,n_features,n_trees,depth", [(1, 3, 1, 1), (37, 6, 9, 4), (300, 40, 50, 6), (64, 150, 20, 9)])
+def test_tree_shap_bit_exact(ops, n_rows, n_features, n_trees, depth):
+    """K10 = the oracle's R13 bit for bit (ragged trees, repeated features on a path, NaN either way), and every
+    row's attributions add up to its margin."""
+    from cobalt_smart_lender_ai_b200.booster import Booster
+    from cobalt_smart_lender_ai_b200.explain import TreeExplainer
+    rng = np.random.default_rng(n_rows)
+    fo, pools = _random_forest(rng, n_trees, n_features, depth, 6)
+    X = rng.normal(size=(n_rows, n_features)).astype(np.float32)
+    X[rng.random(X.shape) < 0.1] = np.nan
+    want = O.tree_shap(X, fo["tree_offsets"], fo["left"], fo["right"], fo["split_index"], fo["split_cond"],
+                       fo["default_left"], fo["sum_hess"], 0.0)
+    b = Booster(fo, n_features, None, 0.5)
+    got = b.predict_contribs_device(_dev(X)).cpu().numpy()
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    margin = b.predict_device(_dev(X), output_margin=True).cpu().numpy()
+    assert np.max(np.abs(got.astype(np.float64).sum(1) - margin)) <= 1e-4 * max(1.0, np.abs(margin).max())
+    ex = TreeExplainer(b)
+    assert np.array_equal(ex.shap_values(X[0]), want[:1, :-1]) and ex.expected_value == float(want[0, -1])
+
+
+def test_tree_shap_fixture_forest(ops, fixture_forest):
+    """The reference's shipped 300-tree model explained on the GPU: oracle bits, additivity to the margin."""
+    from cobalt_smart_lender_ai_b200.booster import Booster
+    ff = fixture_forest
+    rng = np.random.default_rng(11)
+    X = (rng.normal(size=(200, 20)) * 200 + 400).astype(np.float32)
+    X[:, 12:] = rng.integers(0, 2, (200, 8))
+    X[rng.random(X.shape) < 0.05] = np.nan
+    b = Booster(ff, 20, [str(s) for s in ff["feature_names"]], float(ff["base_score"]))
+    got = b.predict_contribs_device(_dev(X)).cpu().numpy()
+    want = O.tree_shap(X, ff["tree_offsets"], ff["left"], ff["right"], ff["split_index"], ff["split_cond"],
+                       ff["default_left"], ff["sum_hess"], 0.0)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    margin = O.predict_margin(X, ff["tree_offsets"], ff["left"], ff["right"], ff["split_index"], ff["split_cond"],
+                              ff["default_left"], 0.0)
+    assert np.max(np.abs(got.astype(np.float64).sum(1) - margin)) <= 2e-4
 
 
 def test_estimator_end_to_end(ops, data):
@@ -603,6 +612,7 @@ def test_scoring_service_on_gpu(ops, fixture_forest, tmp_path):
     path = tmp_path / "model.ubj"
     ubjson.save_model(Booster(ff, 20, names, float(ff["base_score"])), str(path))
     api.xgb_model = api.load_model(path)
+    api.explainer = api.TreeExplainer(api.xgb_model)       # what lifespan() does at start-up (reference :45-46)
     rng = np.random.default_rng(3)
     X = (rng.normal(size=(50, 20)) * 200 + 400).astype(np.float32)
     X[:, 12:] = rng.integers(0, 2, (50, 8))
@@ -618,6 +628,10 @@ def test_scoring_service_on_gpu(ops, fixture_forest, tmp_path):
     row = {n: float(df.iloc[0][n]) for n in names}
     r = client.post("/predict", json=row)
     assert r.status_code == 200 and abs(r.json()["prob_default"] - want[0]) <= 1e-5
+    phi = O.tree_shap(X[:1], ff["tree_offsets"], ff["left"], ff["right"], ff["split_index"], ff["split_cond"],
+                      ff["default_left"], ff["sum_hess"], 0.0)
+    assert np.array_equal(np.array(r.json()["shap_values"], np.float32).view(np.uint32), phi[0, :20].view(np.uint32))
+    assert np.float32(r.json()["base_value"]) == phi[0, 20]
     r = client.post("/feature_importance_bulk", json={"data": [row]})
     assert r.json()["top_features"][0]["feature"] in names
 

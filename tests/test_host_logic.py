@@ -183,7 +183,14 @@ def test_api_routes_with_stub_model():
         def get_booster(self):
             return _Booster()
 
+    class _Explainer:                       # shap.TreeExplainer's surface as /predict uses it (reference :100-105)
+        expected_value = -1.5
+
+        def shap_values(self, df):
+            return np.tile(np.arange(df.shape[1], dtype=np.float32), (len(df), 1))
+
     api.xgb_model = _Stub()
+    api.explainer = _Explainer()
     client = TestClient(api.app)            # no context manager: lifespan (model load) is not run
     fields = {n: 1.0 for n in ("loan_amnt", "term", "installment", "fico_range_low", "last_fico_range_high",
                                "open_il_12m", "open_il_24m", "max_bal_bc", "num_rev_accts", "pub_rec_bankruptcies",
@@ -194,6 +201,7 @@ def test_api_routes_with_stub_model():
     r = client.post("/predict", json=fields)
     assert r.status_code == 200 and r.json()["prob_default"] == 0.25
     assert r.json()["features"][15] == "application_type_Joint App" and len(r.json()["features"]) == 20
+    assert r.json()["shap_values"] == [float(i) for i in range(20)] and r.json()["base_value"] == -1.5
     csv = "a,b\n1,2\n3,\n"
     r = client.post("/predict_bulk_csv", files={"file": ("x.csv", csv, "text/csv")})
     assert r.status_code == 200

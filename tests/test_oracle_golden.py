@@ -218,3 +218,37 @@ def test_oracle_split_rules():
     s2 = O.scan(h2, bp, cuts, mv, -160 - 320, 320 + 320, tp)  # missing carries G=-480,H=320 on feature 0
     assert s2["feature"] == 0 and s2["default_left"] == 1
     assert s2["GL"] + s2["GR"] == -480 and s2["HL"] + s2["HR"] == 640
+
+
+def test_tree_shap_is_the_shapley_value_of_the_path_dependent_expectation():
+    """R13 pinned to its DEFINITION (no shap / xgboost here to compare with): enumerate all feature subsets of small
+    random forests -- ragged trees, features repeated along a path, missing values -- and compare (f64 enumeration
+    vs the f32 algorithm: 1e-5)."""
+    from _forests import random_forest
+    rng = np.random.default_rng(0)
+    for T, F, D in [(3, 4, 3), (5, 6, 4), (4, 5, 5), (2, 3, 6)]:
+        fo, _ = random_forest(rng, T, F, D, 3)
+        X = rng.normal(size=(5, F)).astype(np.float32)
+        X[rng.random(X.shape) < 0.2] = np.nan
+        args = (fo["tree_offsets"], fo["left"], fo["right"], fo["split_index"], fo["split_cond"], fo["default_left"])
+        got = O.tree_shap(X, *args, fo["sum_hess"], 0.5)
+        margin = O.predict_margin(X, *args, 0.5)
+        for r in range(len(X)):
+            phi, base = O.shapley_brute_force(X[r], *args, fo["sum_hess"])
+            assert np.max(np.abs(got[r, :F] - phi)) <= 1e-5
+            assert abs(got[r, F] - 0.5 - base) <= 1e-5
+            assert abs(float(got[r].astype(np.float64).sum()) - margin[r]) <= 1e-5
+
+
+def test_tree_shap_additivity_on_the_shipped_model(fixture_forest):
+    """Local accuracy on the reference's own 300-tree model: attributions + expected value = margin."""
+    ff = fixture_forest
+    rng = np.random.default_rng(4)
+    X = (rng.normal(size=(64, 20)) * 200 + 400).astype(np.float32)
+    X[rng.random(X.shape) < 0.05] = np.nan
+    args = (ff["tree_offsets"], ff["left"], ff["right"], ff["split_index"], ff["split_cond"], ff["default_left"])
+    got = O.tree_shap(X, *args, ff["sum_hess"], 0.0)
+    margin = O.predict_margin(X, *args, 0.0)
+    assert np.max(np.abs(got.astype(np.float64).sum(1) - margin)) <= 2e-4
+    unused = np.setdiff1d(np.arange(20), np.unique(ff["split_index"][ff["left"] != -1]))
+    assert np.all(got[:, unused] == 0.0)                 # a feature no tree splits on gets nothing (dummy axiom)
