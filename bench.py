@@ -341,6 +341,29 @@ def run_ours(args):
                          "h2d_bytes_per_step": int(Xsn.nbytes), "d2h_bytes_per_step": int(pr.nbytes // 2),
                          "what": "XGBClassifier.predict_proba(host X)"}
             del Xsh, Xsn
+        # ---- TreeSHAP (the /predict explanation): same forest, a bounded number of rows
+        if rank == 0 and args.shap_rows > 0:
+            ns = min(args.shap_rows, s1 - s0)
+            booster.predict_contribs_device(Xs[:64])
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            phi = booster.predict_contribs_device(Xs[:ns])
+            e1.record()
+            torch.cuda.synchronize()
+            ms_shap = e0.elapsed_time(e1)
+            shap = {"rows_per_s": round(ns / (ms_shap / 1e3), 1), "rows": ns, "ms": round(ms_shap, 2), "trees": SCORE_TREES,
+                    "additivity_max_err": float((phi.double().sum(1) - booster.predict_device(Xs[:ns], output_margin=True).double()).abs().max())}
+            if not args.no_cpu:
+                from oracle import oracle as O
+                nc_ = min(ns, 256)
+                fo_np = booster.forest
+                t0 = time.perf_counter()
+                O.tree_shap(Xs[:nc_].cpu().numpy(), fo_np["tree_offsets"], fo_np["left"], fo_np["right"], fo_np["split_index"],
+                            fo_np["split_cond"], fo_np["default_left"], fo_np["sum_hess"], 0.0)
+                shap["cpu_rows_per_s"] = round(nc_ / (time.perf_counter() - t0), 1)
+                shap["cpu_sample"] = f"{nc_} rows, oracle R13 with OpenMP on {O.num_threads()} threads"
+            sc["tree_shap"] = shap
         scoring = sc
         del Xs
 
@@ -443,6 +466,7 @@ def main():
     ap.add_argument("--e2e-rounds", type=int, default=ROUNDS_CFG)
     ap.add_argument("--score-rows", type=int, default=SCORE_ROWS)
     ap.add_argument("--score-steps", type=int, default=3)
+    ap.add_argument("--shap-rows", type=int, default=4096, help="rows explained with TreeSHAP in the scoring leg (0: skip)")
     ap.add_argument("--cpu-rounds", type=int, default=8)
     ap.add_argument("--ref-rows", type=int, default=550_000)
     ap.add_argument("--no-e2e", action="store_true")

@@ -238,6 +238,11 @@ def random_forest_like(n_trees: int, depth: int, f: int, seed: int = 78, device=
     dl = torch.randint(0, 2, (n_trees, n_nodes), generator=g, dtype=torch.uint8)
     feat = torch.where(left >= 0, feat, torch.zeros_like(feat))
     offs = torch.arange(n_trees + 1, dtype=torch.int64) * n_nodes
+    cover = torch.zeros((n_trees, n_nodes), dtype=torch.float32)          # node covers for TreeSHAP: leaves draw one,
+    cover[:, n_int:] = 0.25 * torch.randint(1, 200, (n_trees, n_nodes - n_int), generator=g).to(torch.float32)
+    for i in range(n_int - 1, -1, -1):                                    # parents add their children
+        cover[:, i] = cover[:, 2 * i + 1] + cover[:, 2 * i + 2]
     out = {"tree_offsets": offs, "left": left.reshape(-1), "right": right.reshape(-1),
-           "split_index": feat.reshape(-1), "split_cond": cond.reshape(-1), "default_left": dl.reshape(-1)}
+           "split_index": feat.reshape(-1), "split_cond": cond.reshape(-1), "default_left": dl.reshape(-1),
+           "sum_hess": cover.reshape(-1)}
     return {k: v.to(device) for k, v in out.items()}
