@@ -118,6 +118,11 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
         self.importance_type = importance_type
 
     # ------------------------------------------------------------------ helpers
+    def __sklearn_tags__(self):
+        tags = super().__sklearn_tags__()
+        tags.input_tags.allow_nan = True     # missing values are routed by the trees (as xgboost's estimator declares)
+        return tags
+
     def _cuda_device(self) -> torch.device:
         if not torch.cuda.is_available():
             raise _lib.CobaltError("XGBClassifier (cobalt B200 path) needs a CUDA device; there is no CPU fallback")
@@ -139,7 +144,9 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
             raise ValueError("max_bin must be >= 2")
 
     # ------------------------------------------------------------------ fit
-    def fit(self, X, y, sample_weight=None):
+    def _prepare(self, X, y, sample_weight=None) -> dict:
+        """Everything of fit() that does not depend on which features may be split on: H2D, label statistics, K1 cuts,
+        K2 bins (+ the position-major copy).  feature_selection.RFE calls it once and then boosts many times."""
         self._validate_params()
         Xa, names = _as_matrix(X)
         dev = self._cuda_device()
@@ -175,22 +182,41 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
             del Xd
             bins_cm = ops.bin_transpose(bins, blocked=_cf)
             bin_ptr = ops.bin_ptr_of(n_cuts)
-            T = int(self.n_estimators)
-            seed = int(self.random_state or 0)
-            masks = colsample_masks(T, f, float(self.colsample_bytree), seed)
-            masks_d = None if masks is None else torch.from_numpy(masks).to(dev)
-            tr = GpuTrainer(bins, yd, wd, f, bin_ptr, cuts, min_vals, max_depth=int(self.max_depth),
+        return {"dev": dev, "names": names, "n": n, "f": f, "spw": spw, "yd": yd, "wd": wd, "base_score": base_score,
+                "sg": sg, "sh": sh, "row_offset": row_offset, "cuts": cuts, "min_vals": min_vals, "pos": pos, "cf": _cf,
+                "bins": bins, "bins_cm": bins_cm, "bin_ptr": bin_ptr}
+
+    def _boost(self, c: dict, allowed: np.ndarray | None = None) -> dict:
+        """n_estimators rounds on prepared bins -> forest (host arrays).  allowed: u8 [f], features a split may use
+        (None: all); combined with the per-tree colsample masks."""
+        f, dev = c["f"], c["dev"]
+        T = int(self.n_estimators)
+        seed = int(self.random_state or 0)
+        masks = colsample_masks(T, f, float(self.colsample_bytree), seed)
+        if allowed is not None:
+            a = np.ascontiguousarray(allowed, np.uint8).reshape(1, f)
+            masks = np.repeat(a, max(T, 1), axis=0) if masks is None else (masks & a)
+        with torch.cuda.device(dev):
+            masks_d = None if masks is None else torch.from_numpy(np.ascontiguousarray(masks)).to(dev)
+            tr = GpuTrainer(c["bins"], c["yd"], c["wd"], f, c["bin_ptr"], c["cuts"], c["min_vals"], max_depth=int(self.max_depth),
                             eta=float(self.learning_rate), reg_lambda=float(self.reg_lambda),
                             reg_alpha=float(self.reg_alpha), gamma=float(self.gamma),
-                            min_child_weight=float(self.min_child_weight), scale_pos_weight=spw, sg=sg, sh=sh,
+                            min_child_weight=float(self.min_child_weight), scale_pos_weight=c["spw"], sg=c["sg"], sh=c["sh"],
                             subsample=float(self.subsample), seed=seed, max_trees=max(T, 1),
-                            base_margin=base_margin_of(base_score), row_offset=row_offset, pos_feature=pos, blocked=_cf, bins_cm=bins_cm)
+                            base_margin=base_margin_of(c["base_score"]), row_offset=c["row_offset"], pos_feature=c["pos"],
+                            blocked=c["cf"], bins_cm=c["bins_cm"])
             tr.boost(T, masks_d)
             forest = tr.forest_numpy()
             self._gpu_launches = tr.launch_count()
             tr.close()
-        self._Booster = Booster(forest, f, names, base_score,
-                                attributes={"sg": sg, "sh": sh, "scale_pos_weight": spw})
+        return forest
+
+    def fit(self, X, y, sample_weight=None):
+        c = self._prepare(X, y, sample_weight)
+        forest = self._boost(c)
+        f, names = c["f"], c["names"]
+        self._Booster = Booster(forest, f, names, c["base_score"],
+                                attributes={"sg": c["sg"], "sh": c["sh"], "scale_pos_weight": c["spw"]})
         self.classes_ = np.array([0, 1])
         self.n_classes_ = 2
         self.n_features_in_ = f

@@ -636,6 +636,42 @@ def test_scoring_service_on_gpu(ops, fixture_forest, tmp_path):
     assert r.json()["top_features"][0]["feature"] in names
 
 
+def test_rfe_bins_once_and_matches_sklearn_rfe(ops, data):
+    """the elimination loop on resident bins (one sketch + binning, a feature mask per step) selects and
+    ranks exactly like sklearn's RFE refitting the same estimator on every column subset."""
+    import time
+
+    import pandas as pd
+    from sklearn.feature_selection import RFE as SkRFE
+
+    from cobalt_smart_lender_ai_b200.feature_selection import RFE
+    from cobalt_smart_lender_ai_b200.sklearn import XGBClassifier
+    X, y, names = data
+    df = pd.DataFrame(X[:20000, :40], columns=names[:40])
+    yt = pd.Series(y[:20000])
+    base = XGBClassifier(eval_metric="logloss", use_label_encoder=False, scale_pos_weight=3.0, random_state=42,
+                         n_estimators=12, max_depth=4)
+    t0 = time.perf_counter()
+    fast = RFE(estimator=base, n_features_to_select=20, step=1).fit(df, yt)
+    t1 = time.perf_counter()
+    slow = SkRFE(estimator=base, n_features_to_select=20, step=1).fit(df, yt)
+    t2 = time.perf_counter()
+    assert fast.binned_once_ and fast.fits_ == 20
+    assert np.array_equal(fast.support_, slow.support_) and np.array_equal(fast.ranking_, slow.ranking_)
+    assert fast.n_features_ == 20
+    Xs = df.iloc[:64]
+    assert np.array_equal(fast.predict_proba(Xs), slow.predict_proba(Xs))
+    assert list(fast.get_feature_names_out()) == list(slow.get_feature_names_out())
+    print(f"RFE 40 -> 20 on 20000 rows: resident bins {t1 - t0:.2f} s, sklearn refits {t2 - t1:.2f} s")
+    # step > 1 and a fractional target go through the same bookkeeping
+    f2 = RFE(estimator=base, n_features_to_select=0.25, step=3).fit(df, yt)
+    s2 = SkRFE(estimator=base, n_features_to_select=0.25, step=3).fit(df, yt)
+    assert np.array_equal(f2.ranking_, s2.ranking_)
+    # colsample_bytree < 1 is delegated to sklearn's RFE
+    f3 = RFE(estimator=XGBClassifier(n_estimators=3, max_depth=2, colsample_bytree=0.5), n_features_to_select=35).fit(df, yt)
+    assert f3.binned_once_ is False and f3.support_.sum() == 35
+
+
 def test_reference_training_job_flow(ops):
     """The reference's training script, steps 2-7 (leakage drop, split, RFE to 20 features,
     RandomizedSearchCV, test metrics, joblib dump/load), on synthetic loans -- with this package's
