@@ -712,6 +712,7 @@ __global__ void __launch_bounds__(256) bin_rows_q8_kernel(const float* __restric
   const int c = c0 + lane;
   const bool on = c < f;
   const int nc = on ? __ldg(n_cuts + c) : 1;
+  const int nc_max = __reduce_max_sync(0xffffffffu, nc);   // probes with a stride above every table length cannot succeed
   const float* my = tab + lane * 257;
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta, r1 = min(n, r0 + rows_per_cta);
   for (int64_t rb = r0 + warp * 4; rb < r1; rb += 32) {       // 8 warps x 4 rows in flight
@@ -725,6 +726,7 @@ __global__ void __launch_bounds__(256) bin_rows_q8_kernel(const float* __restric
     }
 #pragma unroll
     for (int s = 128; s > 0; s >>= 1) {
+      if (s > nc_max) continue;                              // warp uniform: a slab of one-hot columns needs one probe
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const int probe = lo[u] + s;

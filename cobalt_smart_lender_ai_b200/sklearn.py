@@ -60,6 +60,9 @@ def estimate_base_score(n_pos_w: float, n_neg_w: float) -> float:
     return float(np.float32(1.0 / (1.0 + math.exp(-m0))))
 
 
+_STREAM_BYTES = 256 << 20     # host matrices above this size are scored in double-buffered chunks
+
+
 def _as_matrix(X):
     """DataFrame (float/int/bool columns) / ndarray / CUDA tensor -> (array-like f32, names or None)."""
     names = None
@@ -247,8 +250,43 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
         self._check_names(names)
         dev = self._cuda_device()
         with _LOCK, torch.cuda.device(dev):
+            if isinstance(Xa, np.ndarray) and Xa.nbytes > _STREAM_BYTES:
+                return self._proba_streamed(Xa, dev)
             Xd = _to_device(Xa, dev)
             return self.get_booster().predict_device(Xd)
+
+    def _proba_streamed(self, Xa: np.ndarray, dev) -> torch.Tensor:
+        """Large host matrices: rows go to the GPU in chunks on a copy stream, double buffered, while the previous
+        chunk is scored -- the H2D copy (the slower of the two by far) hides the kernels entirely."""
+        n, f = Xa.shape
+        rows = max(1, _STREAM_BYTES // (4 * f))
+        src = torch.from_numpy(Xa)
+        pinned = src.is_pinned()
+        cur = torch.cuda.current_stream(dev)
+        cs = torch.cuda.Stream(dev)
+        bufs = [torch.empty((rows, f), dtype=torch.float32, device=dev) for _ in range(2)]
+        stage = None if pinned else [torch.empty((rows, f), dtype=torch.float32).pin_memory() for _ in range(2)]
+        copied = [torch.cuda.Event() for _ in range(2)]
+        done = [torch.cuda.Event() for _ in range(2)]
+        out = torch.empty(n, dtype=torch.float32, device=dev)
+        booster = self.get_booster()
+        for k, r0 in enumerate(range(0, n, rows)):
+            r1, b = min(n, r0 + rows), k & 1
+            m = r1 - r0
+            if stage is not None:
+                if k >= 2:
+                    copied[b].synchronize()                 # the staging buffer has left for the device
+                stage[b][:m].copy_(src[r0:r1])
+            with torch.cuda.stream(cs):
+                if k >= 2:
+                    cs.wait_event(done[b])                  # the device buffer has been scored
+                bufs[b][:m].copy_(src[r0:r1] if stage is None else stage[b][:m], non_blocking=True)
+                copied[b].record(cs)
+            cur.wait_event(copied[b])
+            out[r0:r1] = booster.predict_device(bufs[b][:m])
+            done[b].record(cur)
+        cur.synchronize()
+        return out
 
     def predict_proba(self, X) -> np.ndarray:
         p = self._proba_device(X).cpu().numpy()

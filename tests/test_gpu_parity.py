@@ -515,6 +515,22 @@ def test_tree_shap_fixture_forest(ops, fixture_forest):
     assert np.max(np.abs(got.astype(np.float64).sum(1) - margin)) <= 2e-4
 
 
+def test_predict_proba_streams_large_host_matrices(ops, fixture_forest, monkeypatch):
+    """Host matrices above the streaming threshold are scored chunk by chunk behind their own H2D copies (pinned
+    source: direct; pageable source: through pinned staging buffers): same bits as the one-shot path."""
+    import cobalt_smart_lender_ai_b200.sklearn as sk
+    ff = fixture_forest
+    clf = sk.XGBClassifier().load_fixture_forest(ff, [str(s) for s in ff["feature_names"]], float(ff["base_score"]))
+    rng = np.random.default_rng(2)
+    X = (rng.normal(size=(10007, 20)) * 200 + 400).astype(np.float32)
+    X[rng.random(X.shape) < 0.05] = np.nan
+    want = clf.predict_proba(X)
+    monkeypatch.setattr(sk, "_STREAM_BYTES", 20 * 4 * 1000)          # 1000-row chunks: 11 chunks, the last one ragged
+    assert np.array_equal(clf.predict_proba(X), want)                  # pageable source
+    Xp = torch.from_numpy(X).pin_memory()
+    assert np.array_equal(clf.predict_proba(Xp.numpy()), want)         # pinned source
+
+
 def test_estimator_end_to_end(ops, data):
     """fit/predict_proba/predict/feature_importances_/get_score/pickle through the drop-in class."""
     import pickle
