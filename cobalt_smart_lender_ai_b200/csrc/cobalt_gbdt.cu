@@ -589,6 +589,7 @@ struct cb_trainer_s {
   cb_train_buffers buf;
   DeviceInfo di;
   int max_nodes, S, S2, grid, tiles, smem, n_part_tiles, pool_slots, lb_slots;
+  int res_flags, res_scatter, res_final;   // CTAs of the level-tail kernels that are resident at once (whole GPU)
   int2* gpair;
   uint32_t* rows[2];
   int cur;
@@ -727,6 +728,17 @@ int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, v
   t->smem = std::min(budget, t->S) * 8;
   t->grid = std::min(di.sm_count, kMaxGrid);
   t->n_part_tiles = ceil_div(cfg->n_rows, kPartTile);
+  {
+    // persistent level-tail grids = what the GPU holds at once (the serial extra CTA included): one CTA more and a
+    // tile CTA waits for the extra CTA before it even starts (tools/level_trace.py: + 4 us per kernel)
+    int a = 0, b = 0, c = 0;
+    CB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, part_level_flags_kernel, 256, 0));
+    CB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, part_level_scatter_kernel, 256, 0));
+    CB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c, final_apply_kernel, 256, 0));
+    t->res_flags = std::max(2, a * t->di.sm_count);
+    t->res_scatter = std::max(2, b * t->di.sm_count);
+    t->res_final = std::max(2, c * t->di.sm_count);
+  }
   t->cur = 0; t->identity = true; t->tree_index = 0; t->fmask = nullptr; t->launches = 0; t->timing = false; t->profiling = false; t->n_marks = 0;
   memset(&t->pc, 0, sizeof t->pc); t->pc.world = 1;
   plan_tiles_kernel<<<1, 1>>>(buf->bin_ptr, cfg->n_features, budget, t->plan);
@@ -956,12 +968,13 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   const int ident = t->identity ? 1 : 0;
   if (level + 1 < D) {
     uint32_t* rout = t->rows[t->cur ^ 1];
-    const int pgrid = std::min(t->n_part_tiles, t->di.sm_count * 5) + 1;     // 5 CTAs per SM resident: whole waves
+    const int pgrid = std::min(t->n_part_tiles, t->res_flags - 1) + 1;
+    const int sgrid = std::min(t->n_part_tiles, t->res_scatter - 1) + 1;
     part_level_flags_kernel<<<pgrid, 256, 0, s>>>(view, t->buf.bins_cm, rin, ident, n, t->n_part_tiles, lc, t->st,
                                                                 t->buf.cuts, t->buf.min_vals, tree_out(t), t->segs,
                                                                 t->flag_bits, t->tile_cnt, t->group_cnt);
     mark(t, s, "flags+finish");
-    part_level_scatter_kernel<<<pgrid, 256, 0, s>>>(rin, ident, n, t->n_part_tiles, t->segs, t->flag_bits,
+    part_level_scatter_kernel<<<sgrid, 256, 0, s>>>(rin, ident, n, t->n_part_tiles, t->segs, t->flag_bits,
                                                                   t->tile_cnt, t->group_cnt, rout, t->buf.margin, t->st,
                                                                   level, D, t->na, t->plan, t->grid,
                                                                   t->cfg.world_size > 1 ? 1 : 0);
@@ -970,7 +983,7 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
     t->launches += 2;
   } else {
     const int nblk = ceil_div(n, 1024);
-    final_apply_kernel<<<nblk + 1, 256, 0, s>>>(view, t->buf.bins_cm, rin, ident, n, nblk, lc, t->st, t->buf.cuts,
+    final_apply_kernel<<<std::min(nblk, t->res_final - 1) + 1, 256, 0, s>>>(view, t->buf.bins_cm, rin, ident, n, nblk, lc, t->st, t->buf.cuts,
                                                 t->buf.min_vals, tree_out(t), t->segs, t->buf.margin);
     mark(t, s, "final_apply");
     t->launches += 1;
@@ -1085,5 +1098,19 @@ int cb_trainer_node_hist(cb_trainer* t, int node_id, const int64_t** ptr) {
 }
 
 int64_t cb_trainer_launch_count(cb_trainer* t) { return t ? t->launches : 0; }
+
+#ifdef CB_LEVEL_TRACE
+// debug build only (tools/level_trace.py): [4 kernels][2048 CTAs][start, end] %globaltimer stamps of the last launches
+int cb_debug_level_trace(unsigned long long* out_host, int clear) {
+  CB_CUDA(cudaDeviceSynchronize());
+  CB_CUDA(cudaMemcpyFromSymbol(out_host, g_level_trace, sizeof(unsigned long long) * 4 * 2048 * 2));
+  if (clear) {
+    void* p = nullptr;
+    CB_CUDA(cudaGetSymbolAddress(&p, g_level_trace));
+    CB_CUDA(cudaMemset(p, 0, sizeof(unsigned long long) * 4 * 2048 * 2));
+  }
+  return CB_OK;
+}
+#endif
 
 }  // extern "C"

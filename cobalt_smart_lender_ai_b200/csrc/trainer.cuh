@@ -4,6 +4,20 @@
 
 namespace cb {
 
+#ifdef CB_LEVEL_TRACE
+// debug build only (tools/level_trace.py): %globaltimer at the start / end of every CTA of the level-tail kernels
+__device__ unsigned long long g_level_trace[4][2048][2];
+__device__ __forceinline__ unsigned long long level_trace_gt() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+struct LevelTraceScope {
+  int k;
+  __device__ LevelTraceScope(int kernel) : k(kernel) { if (threadIdx.x == 0 && blockIdx.x + blockIdx.y * gridDim.x < 2048) g_level_trace[k][blockIdx.x + blockIdx.y * gridDim.x][0] = level_trace_gt(); }
+  __device__ ~LevelTraceScope() { if (threadIdx.x == 0 && blockIdx.x + blockIdx.y * gridDim.x < 2048) g_level_trace[k][blockIdx.x + blockIdx.y * gridDim.x][1] = level_trace_gt(); }
+};
+#define CB_LEVEL_TRACE_SCOPE(kernel) LevelTraceScope level_trace_scope_(kernel)
+#else
+#define CB_LEVEL_TRACE_SCOPE(kernel)
+#endif
+
 constexpr int kMaxDepth = 9;              // levels 0..8 are split; level nodes <= 256
 constexpr int kMaxLevelNodes = 256;
 
@@ -146,6 +160,7 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
                                                                FeatBest* __restrict__ feat_best,
                                                                const int64_t* __restrict__ tail, TreeState* stw,
                                                                int* __restrict__ group_cnt, int n_groups, PeerCtx pc) {
+  CB_LEVEL_TRACE_SCOPE(0);
   __shared__ long long sg[4], sh[4];
   __shared__ unsigned long long skf[4], skb[4];
   const int i = blockIdx.y;
@@ -517,6 +532,7 @@ __global__ void __launch_bounds__(256) part_level_flags_kernel(BinsView view, co
                                                                const float* __restrict__ min_vals, TreeOut to,
                                                                LevelSegs* segs, uint32_t* __restrict__ flag_bits,
                                                                int* __restrict__ tile_cnt, int* __restrict__ group_cnt) {
+  CB_LEVEL_TRACE_SCOPE(1);
   __shared__ NodeTable nt;
   __shared__ int wsum[8];
   if (c.pc.world > 1) {                             // all ranks' candidates of this level must have arrived
@@ -667,6 +683,7 @@ __global__ void __launch_bounds__(256) part_level_scatter_kernel(const uint32_t*
                                                                  uint32_t* __restrict__ rows_out, float* __restrict__ margin,
                                                                  TreeState* st, int level, int max_depth, NodeArrays na,
                                                                  HistPlan* plan, int grid, int by_hessian) {
+  CB_LEVEL_TRACE_SCOPE(2);
   __shared__ SegCache sc;
   __shared__ int s_Lb[kMaxLevelNodes], s_nl[kMaxLevelNodes];
   __shared__ PlanSmem psm;
@@ -747,13 +764,14 @@ __global__ void __launch_bounds__(256) part_level_scatter_kernel(const uint32_t*
 }
 
 // last level: children are leaves, so rows are not moved; each row takes its child's leaf value.
-// Grid = ceil(n / 256) + 1 (finish CTA).
+// Grid = resident tile CTAs + 1 (finish CTA); the tile CTAs loop over blocks of 1024 positions.
 __global__ void __launch_bounds__(256) final_apply_kernel(BinsView view, const uint8_t* __restrict__ bins_cm,
                                                           const uint32_t* __restrict__ rows_in, int identity,
                                                           int n_rows, int n_blocks, LevelCtx c, TreeState* stw,
                                                           const float* __restrict__ cuts,
                                                           const float* __restrict__ min_vals, TreeOut to, LevelSegs* segs,
                                                           float* __restrict__ margin) {
+  CB_LEVEL_TRACE_SCOPE(3);
   __shared__ NodeTable nt;
   if (c.pc.world > 1) {
     if (threadIdx.x == 0) peer_wait(c.pc, stw, 1, peer_epoch(stw, c.level, 1));
@@ -767,7 +785,8 @@ __global__ void __launch_bounds__(256) final_apply_kernel(BinsView view, const u
   const int n = c.st->lvl_count[c.level];
   const int lane = threadIdx.x & 31;
   constexpr int IT = 4;                                // positions per thread, loads batched
-  const int base = ((int)blockIdx.x - 1) * (blockDim.x * IT) + (threadIdx.x & ~31) * IT;
+  for (int blk = (int)blockIdx.x - 1; blk < n_blocks; blk += (int)gridDim.x - 1) {   // resident CTAs: one table build each
+  const int base = blk * (blockDim.x * IT) + (threadIdx.x & ~31) * IT;
   uint32_t row[IT];
   int seg[IT], code[IT];
 #pragma unroll
@@ -800,6 +819,7 @@ __global__ void __launch_bounds__(256) final_apply_kernel(BinsView view, const u
       if (!left) leaf = nt.leafR[seg[it]];
     }
     margin[row[it]] = __fadd_rn(mg[it], leaf);
+  }
   }
 }
 
