@@ -943,7 +943,6 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   if (!t || level < 0 || level >= t->cfg.tree.max_depth) return fail(CB_ERR_INVALID, "trainer: bad level");
   cudaStream_t s = (cudaStream_t)stream;
   const int D = t->cfg.tree.max_depth;
-  const int nb = level == 0 ? 1 : (1 << (level - 1));
   const int ln = 1 << level;
   const int n = (int)t->cfg.n_rows;
   const int n_groups = ceil_div(t->n_part_tiles, kTileGroup);
