@@ -6,8 +6,10 @@ business (out of scope), everything between them is kept step for ste
   3. 80/20 split, random_state 22 (:92-98)              6. RandomizedSearchCV, 20 draws x 3 folds, roc_auc (:130-166)
   4. scale_pos_weight = neg / pos on y_train (:103-105) 7. evaluation on the test split (:171-179)
 
-``XGBClassifier`` is this package's drop-in.  The search runs with ``n_jobs=1`` by default: every fit is
-GPU bound, and loky workers would each open their own CUDA context on the same device.
+``XGBClassifier`` is this package's drop-in; ``RFE`` and ``RandomizedSearchCV`` are this package's classes with
+sklearn's surface and results, which prepare (upload, sketch, bin) a training matrix once and run the many fits of
+the step on the resident bins.  ``n_jobs`` is accepted and ignored by them: every fit is GPU bound, and loky workers
+would each open their own CUDA context on the same device.
 """
 from __future__ import annotations
 
@@ -15,9 +17,10 @@ import logging
 
 import pandas as pd
 from sklearn.metrics import classification_report, confusion_matrix, roc_auc_score
-from sklearn.model_selection import RandomizedSearchCV, StratifiedKFold, train_test_split
+from sklearn.model_selection import StratifiedKFold, train_test_split
 
 from ..feature_selection import RFE          # sklearn.feature_selection.RFE's surface; bins once
+from ..model_selection import RandomizedSearchCV   # sklearn's surface; every fold is sketched and binned once
 from ..sklearn import XGBClassifier
 
 LEAKAGE_COLS = [
