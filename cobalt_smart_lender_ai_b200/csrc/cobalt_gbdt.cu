@@ -1099,14 +1099,14 @@ int cb_trainer_node_hist(cb_trainer* t, int node_id, const int64_t** ptr) {
 int64_t cb_trainer_launch_count(cb_trainer* t) { return t ? t->launches : 0; }
 
 #ifdef CB_LEVEL_TRACE
-// debug build only (tools/level_trace.py): [4 kernels][2048 CTAs][start, end] %globaltimer stamps of the last launches
+// debug build only (tools/level_trace.py): [6 kernels][2048 CTAs][start, end] %globaltimer stamps of the last launches
 int cb_debug_level_trace(unsigned long long* out_host, int clear) {
   CB_CUDA(cudaDeviceSynchronize());
-  CB_CUDA(cudaMemcpyFromSymbol(out_host, g_level_trace, sizeof(unsigned long long) * 4 * 2048 * 2));
+  CB_CUDA(cudaMemcpyFromSymbol(out_host, g_level_trace, sizeof(unsigned long long) * 6 * 2048 * 2));
   if (clear) {
     void* p = nullptr;
     CB_CUDA(cudaGetSymbolAddress(&p, g_level_trace));
-    CB_CUDA(cudaMemset(p, 0, sizeof(unsigned long long) * 4 * 2048 * 2));
+    CB_CUDA(cudaMemset(p, 0, sizeof(unsigned long long) * 6 * 2048 * 2));
   }
   return CB_OK;
 }

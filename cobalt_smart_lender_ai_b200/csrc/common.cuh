@@ -119,6 +119,20 @@ __device__ __forceinline__ double calc_weight(double G, double H, const cb_tree_
   return __ddiv_rn(-t, __dadd_rn(H, (double)p.reg_lambda));
 }
 
+#ifdef CB_LEVEL_TRACE
+// debug build only (tools/level_trace.py): %globaltimer at the start / end of every CTA of the level-tail kernels
+__device__ unsigned long long g_level_trace[6][2048][2];
+__device__ __forceinline__ unsigned long long level_trace_gt() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+struct LevelTraceScope {
+  int k;
+  __device__ LevelTraceScope(int kernel) : k(kernel) { if (threadIdx.x == 0 && blockIdx.x + blockIdx.y * gridDim.x < 2048) g_level_trace[k][blockIdx.x + blockIdx.y * gridDim.x][0] = level_trace_gt(); }
+  __device__ ~LevelTraceScope() { if (threadIdx.x == 0 && blockIdx.x + blockIdx.y * gridDim.x < 2048) g_level_trace[k][blockIdx.x + blockIdx.y * gridDim.x][1] = level_trace_gt(); }
+};
+#define CB_LEVEL_TRACE_SCOPE(kernel) LevelTraceScope level_trace_scope_(kernel)
+#else
+#define CB_LEVEL_TRACE_SCOPE(kernel)
+#endif
+
 constexpr int kChunkRows = 16352;  // rows per int32 partial histogram: 16352 * 2^17 < 2^31
 constexpr int kPartTile = 1024;    // positions per partition tile
 

@@ -163,6 +163,7 @@ hist_accum_cf_kernel(const uint8_t* __restrict__ bins, int64_t n_rows, int last_
                      const uint32_t* __restrict__ row_idx, const HistPlan* __restrict__ plan,
                      const CfLayout* __restrict__ lay, const int32_t* __restrict__ fold_src,
                      const int32_t* __restrict__ fold_dst, int32_t* __restrict__ partials) {
+  CB_LEVEL_TRACE_SCOPE(5);
   extern __shared__ int32_t smem[];
   const int slot = plan->cta_slot[blockIdx.x];
   if (slot < 0) return;
@@ -239,6 +240,7 @@ __global__ void __launch_bounds__(256) hist_reduce_cf_kernel(const int32_t* __re
                                                              const HistPlan* __restrict__ plan, int R, int S,
                                                              const int32_t* __restrict__ slot_of,
                                                              int64_t* __restrict__ level_buf) {
+  CB_LEVEL_TRACE_SCOPE(4);
   const int j = blockIdx.y;
   if (j >= plan->n_build) return;
   const int RW = R * 32;

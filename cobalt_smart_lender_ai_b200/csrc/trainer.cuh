@@ -4,19 +4,6 @@
 
 namespace cb {
 
-#ifdef CB_LEVEL_TRACE
-// debug build only (tools/level_trace.py): %globaltimer at the start / end of every CTA of the level-tail kernels
-__device__ unsigned long long g_level_trace[4][2048][2];
-__device__ __forceinline__ unsigned long long level_trace_gt() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
-struct LevelTraceScope {
-  int k;
-  __device__ LevelTraceScope(int kernel) : k(kernel) { if (threadIdx.x == 0 && blockIdx.x + blockIdx.y * gridDim.x < 2048) g_level_trace[k][blockIdx.x + blockIdx.y * gridDim.x][0] = level_trace_gt(); }
-  __device__ ~LevelTraceScope() { if (threadIdx.x == 0 && blockIdx.x + blockIdx.y * gridDim.x < 2048) g_level_trace[k][blockIdx.x + blockIdx.y * gridDim.x][1] = level_trace_gt(); }
-};
-#define CB_LEVEL_TRACE_SCOPE(kernel) LevelTraceScope level_trace_scope_(kernel)
-#else
-#define CB_LEVEL_TRACE_SCOPE(kernel)
-#endif
 
 constexpr int kMaxDepth = 9;              // levels 0..8 are split; level nodes <= 256
 constexpr int kMaxLevelNodes = 256;

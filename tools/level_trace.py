@@ -44,8 +44,8 @@ lib.cb_debug_level_trace.restype = C.c_int
 lib.cb_debug_level_trace.argtypes = [C.c_void_p, C.c_int]
 tr.boost(6, use_graph=False)
 stream = torch.cuda.current_stream().cuda_stream
-buf = np.zeros((4, 2048, 2), dtype=np.uint64)
-names = ["scan", "flags+finish", "scatter+plan", "final_apply"]
+buf = np.zeros((6, 2048, 2), dtype=np.uint64)
+names = ["scan", "flags+finish", "scatter+plan", "final_apply", "hist_reduce", "hist_accum"]
 _lib.check(lib.cb_debug_level_trace(buf.ctypes.data, 1))
 for tree in range(6, 8):
     _lib.check(lib.cb_trainer_round_begin(tr.handle, tree, None, stream))
@@ -54,14 +54,14 @@ for tree in range(6, 8):
         _lib.check(lib.cb_trainer_level_split(tr.handle, level, stream))
         _lib.check(lib.cb_debug_level_trace(buf.ctypes.data, 1))
         t = buf.astype(np.int64)
-        for k in range(4):
+        for k in (5, 4, 0, 1, 2, 3):
             a = t[k][(t[k][:, 0] > 0) & (t[k][:, 1] > 0)]
             if not len(a):
                 continue
             t0 = a[:, 0].min()
             dur = (a[:, 1] - a[:, 0]) / 1e3
-            special = f"block0 {dur[0]:5.1f} us (ends at {(a[0, 1] - t0) / 1e3:5.1f})" if k > 0 else ""
-            rest = dur[1:] if k > 0 and len(dur) > 1 else dur
+            special = f"block0 {dur[0]:5.1f} us (ends at {(a[0, 1] - t0) / 1e3:5.1f})" if k in (1, 2, 3) else ""
+            rest = dur[1:] if k in (1, 2, 3) and len(dur) > 1 else dur
             print(f"tree {tree} level {level} {names[k]:13s}: ctas {len(a):4d} span {(a[:, 1].max() - t0) / 1e3:6.1f} us | "
                   f"cta med {np.median(rest):5.1f} max {rest.max():5.1f} us | last start +{(a[:, 0].max() - t0) / 1e3:5.1f} us | {special}")
     _lib.check(lib.cb_trainer_round_end(tr.handle, stream))
