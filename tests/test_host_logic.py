@@ -230,3 +230,50 @@ def test_bench_reference_arm_contract():
         assert k in d, k
     assert d["impl"] == "reference" and d["metric"] == "boosting rounds/s" and d["value"] > 0
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["cpu_baseline"]["kind"] == "port" and "workload" in d["config"]
+
+
+def test_q8_forest_encoding_decides_like_the_float_compare():
+    """Host side of the quantised scorer (booster.q8_forest): threshold tables, node words (span << 16 | plane/feature
+    offset) and the two code planes, walked here in numpy exactly as predict_q8_kernel does, give the oracle's margins
+    bit for bit -- values on / next to thresholds, +-inf, -0.0 and NaN with either default direction."""
+    from _forests import random_forest
+
+    from cobalt_smart_lender_ai_b200.booster import heap_forest, q8_forest
+    from oracle import oracle as O
+    rng = np.random.default_rng(1)
+    for n, f, T, depth, base in [(200, 7, 9, 3, 0), (300, 150, 20, 6, 1024), (100, 250, 5, 6, 1024)]:
+        fo, pools = random_forest(rng, T, f, depth, 40)
+        X = np.zeros((n, f), np.float32)
+        for j in range(f):
+            b = rng.choice(pools[j], size=n)
+            kind = rng.integers(0, 6, size=n)
+            X[:, j] = np.where(kind == 0, b, np.where(kind == 1, np.nextafter(b, np.float32(-np.inf)),
+                               np.where(kind == 2, np.nextafter(b, np.float32(np.inf)), rng.normal(size=n)))).astype(np.float32)
+        for val, p in ((np.nan, 0.08), (np.inf, 0.01), (-np.inf, 0.01), (-0.0, 0.01)):
+            X[rng.random(X.shape) < p] = val
+        args = (fo["tree_offsets"], fo["left"], fo["right"], fo["split_index"], fo["split_cond"], fo["default_left"])
+        want = O.predict_margin(X, *args, 0.0)
+        thr, meta, leaf, d = heap_forest(*args)
+        cuts, n_cuts, words = q8_forest(thr, meta, leaf, d, f, base)
+        codes = np.full((n, f), 255, np.int64)                      # K2: number of thresholds <= x, clamped; NaN -> 255
+        for j in range(f):
+            c = cuts[j, :n_cuts[j]]
+            lo = np.searchsorted(c, X[:, j], side="right")
+            codes[:, j] = np.where(np.isnan(X[:, j]), 255, np.minimum(lo, n_cuts[j] - 1))
+        planes = np.stack([codes, (codes + 1) & 255])               # plane 1: code + 1, missing wraps to 0
+        m = np.zeros(n, np.float32)
+        rows = np.arange(n)
+        for t in range(words.shape[0]):
+            i = np.ones(n, np.int64)
+            for _ in range(d):
+                q = words[t, i].astype(np.int64)
+                off = ((q & 0xFFFF) - base) // 128                  # (plane * f + feature)
+                x = planes[off // f, rows, off % f]
+                i = 2 * i + np.where((x << 16) <= q, 0, 1)
+            m = (m + words[t, i].view(np.float32)).astype(np.float32)
+        assert np.array_equal(m.view(np.uint32), want.view(np.uint32))
+    # more thresholds on a feature than a byte can index: no quantised form
+    fo, _ = random_forest(rng, 400, 2, 6, 4000)
+    thr, meta, leaf, d = heap_forest(fo["tree_offsets"], fo["left"], fo["right"], fo["split_index"], fo["split_cond"],
+                                     fo["default_left"])
+    assert q8_forest(thr, meta, leaf, d, 2, 1024) is None
