@@ -252,3 +252,22 @@ def test_tree_shap_additivity_on_the_shipped_model(fixture_forest):
     assert np.max(np.abs(got.astype(np.float64).sum(1) - margin)) <= 2e-4
     unused = np.setdiff1d(np.arange(20), np.unique(ff["split_index"][ff["left"] != -1]))
     assert np.all(got[:, unused] == 0.0)                 # a feature no tree splits on gets nothing (dummy axiom)
+
+
+def test_training_rules_learn_like_an_independent_histogram_gbdt():
+    """Training end to end is unpinned against xgboost (not installable); as an independent cross-check
+    the restated rules R1-R10 must reach the held-out AUC of sklearn's HistGradientBoostingClassifier -- another
+    histogram GBDT with different binning and growth details -- within a sanity band."""
+    from sklearn.ensemble import HistGradientBoostingClassifier
+    from sklearn.metrics import roc_auc_score
+
+    from cobalt_smart_lender_ai_b200.synth import make_lending
+    X, y, _ = make_lending(24000, 30, seed=5)
+    X, y = X.numpy(), y.numpy().astype(int)
+    Xtr, ytr, Xte, yte = X[:16000], y[:16000], X[16000:], y[16000:]
+    ref = O.fit_reference(Xtr, ytr, n_estimators=60, max_depth=6, learning_rate=0.1, scale_pos_weight=1.0)
+    auc_oracle = roc_auc_score(yte, O.predict_proba_reference(ref, Xte))
+    hgb = HistGradientBoostingClassifier(max_iter=60, max_depth=6, max_leaf_nodes=None, learning_rate=0.1, l2_regularization=1.0,
+                                         min_samples_leaf=1, max_bins=255, early_stopping=False).fit(Xtr, ytr)
+    auc_hgb = roc_auc_score(yte, hgb.predict_proba(Xte)[:, 1])
+    assert auc_oracle > 0.7 and abs(auc_oracle - auc_hgb) <= 0.01, (auc_oracle, auc_hgb)
