@@ -277,3 +277,33 @@ def test_q8_forest_encoding_decides_like_the_float_compare():
     thr, meta, leaf, d = heap_forest(fo["tree_offsets"], fo["left"], fo["right"], fo["split_index"], fo["split_cond"],
                                      fo["default_left"])
     assert q8_forest(thr, meta, leaf, d, 2, 1024) is None
+
+
+def test_orchestration_classes_delegate_what_they_do_not_cover():
+    """feature_selection.RFE / model_selection.RandomizedSearchCV take the prepared-once path only for this package's
+    estimator (and roc_auc for the search); anything else is handed to sklearn's own classes unchanged."""
+    from sklearn.feature_selection import RFE as SkRFE
+    from sklearn.linear_model import LogisticRegression
+    from sklearn.model_selection import RandomizedSearchCV as SkSearch
+
+    from cobalt_smart_lender_ai_b200.feature_selection import RFE
+    from cobalt_smart_lender_ai_b200.model_selection import RandomizedSearchCV
+    from cobalt_smart_lender_ai_b200.sklearn import XGBClassifier
+    rng = np.random.default_rng(0)
+    X = rng.normal(size=(300, 8))
+    y = (X[:, 0] + 0.5 * X[:, 3] + 0.2 * rng.normal(size=300) > 0).astype(int)
+    lr = LogisticRegression(max_iter=200)
+    a = RFE(estimator=lr, n_features_to_select=3).fit(X, y)
+    b = SkRFE(estimator=lr, n_features_to_select=3).fit(X, y)
+    assert a.binned_once_ is False and np.array_equal(a.support_, b.support_) and np.array_equal(a.ranking_, b.ranking_)
+    assert a.transform(X).shape == (300, 3)
+    kw = dict(param_distributions={"C": [0.1, 1.0, 10.0]}, n_iter=2, scoring="roc_auc", cv=3, random_state=0)
+    s1 = RandomizedSearchCV(estimator=lr, **kw).fit(X, y)
+    s2 = SkSearch(estimator=lr, **kw).fit(X, y)
+    assert s1.prepared_folds_ is None and s1.best_params_ == s2.best_params_ and s1.best_score_ == s2.best_score_
+    assert np.array_equal(s1.predict(X), s2.predict(X))
+    # which settings take the fast path
+    assert RFE(estimator=XGBClassifier(), n_features_to_select=3)._fast_path()
+    assert not RFE(estimator=XGBClassifier(colsample_bytree=0.5), n_features_to_select=3)._fast_path()
+    assert RandomizedSearchCV(XGBClassifier(), {}, scoring="roc_auc")._fast_path()
+    assert not RandomizedSearchCV(XGBClassifier(), {}, scoring="accuracy")._fast_path()
