@@ -888,7 +888,9 @@ int cb_trainer_level_hist(cb_trainer* t, int level, void* stream) {
   const int nb = level == 0 ? 1 : (1 << (level - 1));
   if (t->cf) {
     const int gx = ceil_div(t->cf_R * 32 / 4, 256);
-    int nz = (2 * t->di.sm_count) / (gx * nb);
+    // z-slices per node: the partials are spread unevenly over the nodes (CTAs follow the rows), and the slice count
+    // is what bounds the longest chain of a big node's CTAs; empty slices of small nodes exit at once
+    int nz = std::max((2 * t->di.sm_count) / (gx * nb), 64 / nb);
     nz = nz < 1 ? 1 : (nz > 16 ? 16 : nz);
     if (nz > 1) CB_CUDA(cudaMemsetAsync(t->level_buf, 0, sizeof(int64_t) * (size_t)nb * t->S2, s));
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
