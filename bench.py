@@ -398,6 +398,7 @@ def run_ours(args):
                 "clocks": clk.summary(), "scoring": scoring, "prep_ms": round(t_prep, 2), "train_auc_200k": auc}
         print(json.dumps(line), file=_OUT, flush=True)
     if world > 1:
+        torch.distributed.barrier()               # rank 0 has the extra legs (TreeSHAP, printing): leave together
         torch.distributed.destroy_process_group()
 
 
