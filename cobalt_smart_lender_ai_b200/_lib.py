@@ -57,20 +57,38 @@ def sources() -> list[str]:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compiles csrc/cobalt_gbdt.cu for sm_100a with nvcc (cross-compiles without a GPU)."""
+    """Compiles csrc/cobalt_gbdt.cu for sm_100a with nvcc (cross-compiles without a GPU).
+
+    Safe with one process per GPU: an flock serialises the builders, the staleness check is repeated under the lock, and
+    nvcc writes to a temporary file that is renamed into place, so no rank ever dlopens a half-written library."""
     srcs = sources()
-    if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(s) for s in srcs):
+
+    def fresh() -> bool:
+        return os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(s) for s in srcs)
+    if not force and fresh():
         return LIB_PATH
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(nvcc):
         raise CobaltError("libcobalt_gbdt.so is missing or stale and nvcc was not found to rebuild it")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH,
-                                                                          os.path.join(_CSRC, "cobalt_gbdt.cu")]
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        raise CobaltError("nvcc failed:\n" + res.stderr[-4000:])
-    if verbose:
-        print(res.stderr)
+    import fcntl
+    with open(LIB_PATH + ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and fresh():          # another process built it while we waited
+                return LIB_PATH
+            tmp = f"{LIB_PATH}.tmp.{os.getpid()}"
+            cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", tmp,
+                                                                                  os.path.join(_CSRC, "cobalt_gbdt.cu")]
+            res = subprocess.run(cmd, capture_output=True, text=True)
+            if res.returncode != 0:
+                if os.path.exists(tmp):
+                    os.unlink(tmp)
+                raise CobaltError("nvcc failed:\n" + res.stderr[-4000:])
+            os.replace(tmp, LIB_PATH)
+            if verbose:
+                print(res.stderr)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
     return LIB_PATH
 
 

@@ -30,17 +30,20 @@ explainer = None
 
 
 def load_model(path) -> object:
-    """joblib pickle of this package's estimator, else an xgboost pickle / .ubj decoded without xgboost."""
+    """An xgboost pickle / .ubj is decoded without xgboost and WITHOUT executing the pickle (``ubjson.py`` scans the
+    opcodes for the booster payload); only a file that holds no booster payload -- i.e. this package's own estimator
+    pickle -- is handed to ``joblib.load``."""
     import joblib
 
-    from ..ubjson import load_xgboost_pickle
+    from ..ubjson import NoBoosterPayload, load_xgboost_pickle
     try:
-        model = joblib.load(path)
-        if hasattr(model, "predict_proba") and type(model).__module__.startswith("cobalt_smart_lender_ai_b200"):
-            return model
-    except Exception:
+        return load_xgboost_pickle(str(path))
+    except NoBoosterPayload:
         pass
-    return load_xgboost_pickle(str(path))
+    model = joblib.load(path)
+    if not (hasattr(model, "predict_proba") and type(model).__module__.startswith("cobalt_smart_lender_ai_b200")):
+        raise TypeError(f"{path}: neither an xgboost booster payload nor a pickle of this package's XGBClassifier")
+    return model
 
 
 @asynccontextmanager
@@ -112,7 +115,9 @@ async def predict_bulk_csv(file: UploadFile = File(...)):
         contents = await file.read()
         df = pd.read_csv(BytesIO(contents))
         df["prob_default"] = predict_proba_df(df)
-        df_clean = df.replace([np.inf, -np.inf], np.nan).astype(object).where(df.notna(), "null")
+        # reference :121: replace([inf, -inf], nan).fillna("null") -- the mask must come from the REPLACED frame
+        d = df.replace([np.inf, -np.inf], np.nan)
+        df_clean = d.astype(object).where(d.notna(), "null")
         return {"predictions": df_clean.to_dict(orient="records")}
     except Exception as e:
         print(f"[ERROR] Bulk prediction failed: {e}")

@@ -91,7 +91,11 @@ def _to_device(a, device) -> torch.Tensor:
 
 
 class XGBClassifier(ClassifierMixin, BaseEstimator):
-    """Binary logistic histogram GBDT with xgboost's estimator interface and defaults."""
+    """Binary logistic histogram GBDT with xgboost's estimator interface and defaults.
+
+    ``max_bin``: bin codes are one byte and code 255 is reserved for missing values, so a feature gets at most 255
+    real bins: ``max_bin=256`` (xgboost's default and the shipped model's setting) is accepted and means 255 here (a
+    declared deviation); larger values are refused rather than silently clamped."""
 
     def __init__(self, n_estimators=100, max_depth=6, learning_rate=0.3, subsample=1.0, colsample_bytree=1.0,
                  gamma=0.0, scale_pos_weight=1.0, random_state=0, eval_metric=None, use_label_encoder=None,
@@ -143,8 +147,8 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
             raise ValueError("only missing=nan is implemented")
         if not 1 <= int(self.max_depth) <= 9:
             raise ValueError("max_depth must be in [1, 9]")
-        if int(self.max_bin) < 2:
-            raise ValueError("max_bin must be >= 2")
+        if not 2 <= int(self.max_bin) <= 256:
+            raise ValueError("max_bin must be in [2, 256] (one-byte bin codes; 256 means 255 real bins + the missing code)")
 
     # ------------------------------------------------------------------ fit
     def _prepare(self, X, y, sample_weight=None) -> dict:

@@ -98,18 +98,27 @@ def decode(buf: bytes):
     return value()
 
 
+class NoBoosterPayload(ValueError):
+    """The file holds no xgboost booster buffer (it may be a pickle of this package's own estimator)."""
+
+
 def booster_bytes(path: str) -> bytes:
-    """The xgboost Booster's raw buffer inside a pickle (largest bytes constant), or the file itself."""
+    """The xgboost Booster's raw buffer inside a pickle (largest bytes constant that opens a UBJSON object), or the
+    file itself.  The pickle is only scanned opcode by opcode, never executed."""
     with open(path, "rb") as fh:
         data = fh.read()
     if data[:1] == b"{":
         return data
     best = b""
-    for op, arg, _ in pickletools.genops(data):
-        if arg is not None and op.name.startswith(("BINBYTES", "SHORT_BINBYTES", "BYTEARRAY")) and len(arg) > len(best):
-            best = bytes(arg)
+    try:
+        for op, arg, _ in pickletools.genops(data):
+            if (arg is not None and op.name.startswith(("BINBYTES", "SHORT_BINBYTES", "BYTEARRAY")) and len(arg) > len(best)
+                    and bytes(arg[:1]) == b"{" and b"learner" in bytes(arg[:4096])):
+                best = bytes(arg)
+    except Exception:          # not a plain pickle stream (e.g. joblib's interleaved array payloads): keep what was found
+        pass
     if not best:
-        raise ValueError(f"{path}: no booster payload found")
+        raise NoBoosterPayload(f"{path}: no booster payload found")
     return best
 
 

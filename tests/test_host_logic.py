@@ -207,6 +207,12 @@ def test_api_routes_with_stub_model():
     assert r.status_code == 200
     recs = r.json()["predictions"]
     assert len(recs) == 2 and recs[0]["prob_default"] == 0.25 and recs[1]["b"] == "null"
+    # +-inf and empty cells all come back as the string "null" (reference :121 replace([inf, -inf], nan).fillna("null"))
+    csv = "a,b\ninf,2\n-inf,\n5,7\n"
+    r = client.post("/predict_bulk_csv", files={"file": ("x.csv", csv, "text/csv")})
+    assert r.status_code == 200, r.text
+    recs = r.json()["predictions"]
+    assert recs[0]["a"] == "null" and recs[1]["a"] == "null" and recs[1]["b"] == "null" and recs[2]["a"] == 5.0
     r = client.post("/feature_importance_bulk", json={"data": [{"x": 1}]})
     top = r.json()["top_features"]
     assert len(top) == 10 and top[0] == {"feature": "f14", "importance": 14.0}
@@ -307,3 +313,35 @@ def test_orchestration_classes_delegate_what_they_do_not_cover():
     assert not RFE(estimator=XGBClassifier(colsample_bytree=0.5), n_features_to_select=3)._fast_path()
     assert RandomizedSearchCV(XGBClassifier(), {}, scoring="roc_auc")._fast_path()
     assert not RandomizedSearchCV(XGBClassifier(), {}, scoring="accuracy")._fast_path()
+
+
+def test_load_model_never_unpickles_a_foreign_file(tmp_path, fixture_forest):
+    """load_model scans for an xgboost booster payload first (no code of the file runs) and only unpickles files that
+    hold none -- this package's own estimator, saved with joblib or pickle."""
+    import pickle
+
+    import joblib
+
+    from cobalt_smart_lender_ai_b200.api.cobalt_fast_api import load_model
+    from cobalt_smart_lender_ai_b200.sklearn import XGBClassifier
+    from cobalt_smart_lender_ai_b200 import ubjson
+    keys = ["tree_offsets", "left", "right", "parent", "split_index", "split_cond", "default_left", "base_weight",
+            "loss_chg", "sum_hess"]
+    m = XGBClassifier().load_fixture_forest({k: fixture_forest[k] for k in keys},
+                                            [str(x) for x in fixture_forest["feature_names"]], 0.5)
+    a, b = tmp_path / "a.pkl", tmp_path / "b.pkl"
+    joblib.dump(m, a)
+    b.write_bytes(pickle.dumps(m))
+    for p in (a, b):
+        with pytest.raises(ubjson.NoBoosterPayload):
+            ubjson.booster_bytes(str(p))
+        got = load_model(p)
+        assert np.array_equal(got.get_booster().forest["split_cond"], fixture_forest["split_cond"])
+
+    class Evil:
+        def __reduce__(self):
+            return (os.system, ("exit 1",))
+    c = tmp_path / "c.pkl"
+    c.write_bytes(pickle.dumps({"x": Evil()}))
+    with pytest.raises(Exception):
+        load_model(c)          # joblib.load is reached only for payload-free files; a foreign object is refused
