@@ -38,7 +38,7 @@ def _peaks():
 
 
 class ClockSampler:
-    """SM clock + throttle reasons sampled every 20 ms while the timed region runs.
+    """SM clock + throttle reasons sampled every 2 ms while the timed region runs.
 
     NVML in-process (the library nvidia-smi itself reads; handle opened BEFORE the timed region): starting an
     `nvidia-smi -lms` process inside a 100-ms timed region enumerates all 8 GPUs of the box under a driver lock and
@@ -72,7 +72,7 @@ class ClockSampler:
                 self.samples.append((mhz, self.max_mhz, [bool(r & b) for b in bits]))
             except Exception:
                 pass
-            self._stop.wait(0.02)
+            self._stop.wait(0.002)
 
     def _poll_smi(self):
         for l in self.proc.stdout:
@@ -149,6 +149,141 @@ def _timed(fn, world, dev):
     return float(ms.item())
 
 
+def _config(n_rows, steps, warmup, world):
+    """the `config` object: the workload, identical in both arms (the driver compares them)"""
+    return {"workload": WORKLOAD, "rows": n_rows, "features": N_FEAT, "max_bin": 256, "max_depth": DEPTH,
+            "rounds_window": f"rounds {warmup + 1}..{warmup + steps} of one fit from margin 0 (early rounds scan the most rows per level)",
+            "l2_policy": "inputs larger than L2 (binned matrix vs 126 MB L2)" if world == 1 else
+            "binned shard may fit L2 at N>=4 (strong scaling of one matrix)",
+            "parallelism": f"rows sharded x{world}, one exchange of the level's histograms per tree level" if world > 1 else "single GPU"}
+
+
+def _slice_forest(flat: dict, k: int) -> dict:
+    """first k trees of a flat wire-format forest"""
+    offs = flat["tree_offsets"][: k + 1]
+    out = {"tree_offsets": offs}
+    for key, v in flat.items():
+        if key not in ("tree_offsets", "n_nodes"):
+            out[key] = v[: int(offs[-1])]
+    return out
+
+
+def _forest_equal(a: dict, b: dict) -> bool:
+    import numpy as np
+    ok = True
+    for k in ("tree_offsets", "left", "right", "split_index", "split_bin", "default_left"):
+        ok &= bool(np.array_equal(a[k], b[k]))
+    for k in ("split_cond", "base_weight", "loss_chg", "sum_hess"):
+        ok &= bool(np.array_equal(np.asarray(a[k], np.float32).view(np.uint32), np.asarray(b[k], np.float32).view(np.uint32)))
+    return ok
+
+
+def _forest_parity(O, fo_gpu: dict, oracle_parts: list, k: int, n_feat: int, dev, n_rows: int) -> dict:
+    """GPU forest (first k trees) vs the oracle's k trees grown from the same bins and start margin: bitwise equality,
+    then max |dp| and |dAUC| of the two forests on 65 536 held-out synthetic rows (targets 1e-5 / 1e-4)."""
+    import numpy as np
+    import torch
+    from sklearn.metrics import roc_auc_score
+
+    from cobalt_smart_lender_ai_b200.booster import Booster
+    from cobalt_smart_lender_ai_b200.synth import make_lending
+    flats = [O.flatten_forest(p) for p in oracle_parts]
+    offs = [0]
+    for fl in flats:
+        offs += [int(o) + offs[-1] for o in fl["tree_offsets"][1:]]
+    ref = {"tree_offsets": np.asarray(offs, np.int64)}
+    for key in flats[0]:
+        if key != "tree_offsets":
+            ref[key] = np.concatenate([f[key] for f in flats])
+    got = _slice_forest(fo_gpu, k)
+    equal = _forest_equal(got, ref)
+    Xh, yh, _ = make_lending(65536, n_feat, row_offset=n_rows + 1_000_000, device=dev)
+    p_gpu = Booster(got, n_feat, None, 0.5).predict_device(Xh).cpu().numpy()
+    m_cpu = O.predict_margin(Xh.cpu().numpy(), ref["tree_offsets"], ref["left"], ref["right"], ref["split_index"],
+                             ref["split_cond"], ref["default_left"], 0.0)
+    p_cpu = O.sigmoid(m_cpu)
+    yy = yh.cpu().numpy()
+    return {"config": f"{n_rows} x {n_feat} (the benchmarked matrix), trees 1..{k}", "trees": k, "forest_equal": bool(equal),
+            "max_dp": float(np.max(np.abs(p_gpu - p_cpu))), "dauc": float(abs(roc_auc_score(yy, p_gpu) - roc_auc_score(yy, p_cpu))),
+            "held_out_rows": 65536, "targets": {"max_dp": 1e-5, "dauc": 1e-4}}
+
+
+def _hgb_baseline(n_rows: int, n_feat: int, depth: int, dev) -> dict:
+    """sklearn HistGradientBoostingClassifier on the host cores, full matrix, a bounded number of iterations.
+    An independent hist-GBDT (different binning, no parity claim); rounds/s = extra iterations / extra seconds between a
+    2-iteration and an 8-iteration fit, so its one-off binning is not charged to the rounds."""
+    import numpy as np
+    from sklearn.ensemble import HistGradientBoostingClassifier as HGB
+
+    from cobalt_smart_lender_ai_b200.synth import make_lending
+    X, y, _ = make_lending(n_rows, n_feat, device=dev)
+    X, y = X.cpu().numpy(), y.cpu().numpy()
+    kw = dict(max_depth=depth, max_leaf_nodes=None, learning_rate=ETA, l2_regularization=1.0, min_samples_leaf=1,
+              max_bins=255, early_stopping=False)
+    ts = []
+    for it in (2, 8):
+        t0 = time.perf_counter()
+        m = HGB(max_iter=it, **kw).fit(X, y)
+        ts.append(time.perf_counter() - t0)
+    ns = min(n_rows, 1_000_000)
+    t0 = time.perf_counter()
+    m.predict_proba(X[:ns])
+    tpred = time.perf_counter() - t0
+    return {"value": round(6 / max(ts[1] - ts[0], 1e-9), 3), "unit": "rounds/s", "cores": os.cpu_count(), "kind": "sklearn-HGB stand-in",
+            "sample": f"full {n_rows} x {n_feat}; (8-iteration fit - 2-iteration fit) / 6; fits took {ts[0]:.1f} s and {ts[1]:.1f} s",
+            "predict_rows_per_s_8_trees": round(ns / tpred, 0)}
+
+
+def _config_c0(O, dev) -> dict:
+    """BASELINE.json configs[0]: 100k x 100, the training job's default classifier (100 trees, depth 6, eta 0.3),
+    train + predict on the CPU (oracle port and sklearn HGB) and through this package's estimator from host arrays;
+    the GPU forest must equal the oracle's."""
+    import numpy as np
+    import torch
+    from sklearn.ensemble import HistGradientBoostingClassifier as HGB
+    from sklearn.metrics import roc_auc_score
+
+    from cobalt_smart_lender_ai_b200.sklearn import XGBClassifier
+    from cobalt_smart_lender_ai_b200.synth import make_lending
+    n, f, T = 100_000, 100, 100
+    X, y, _ = make_lending(n, f, seed=7, device=dev)
+    X, y = X.cpu().numpy(), y.cpu().numpy()
+    spw = float((y == 0).sum() / (y == 1).sum())
+    out = {"workload": "100k x 100, 100 trees, depth 6, eta 0.3 (configs[0])"}
+    t0 = time.perf_counter()
+    ref = O.fit_reference(X, y, n_estimators=T, max_depth=6, scale_pos_weight=spw)
+    t_fit = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    p_ref = O.predict_proba_reference(ref, X)
+    t_pr = time.perf_counter() - t0
+    out["oracle_port"] = {"fit_rounds_per_s": round(T / t_fit, 2), "predict_rows_per_s": round(n / t_pr, 0), "cores": O.num_threads()}
+    t0 = time.perf_counter()
+    m = HGB(max_iter=T, max_depth=6, max_leaf_nodes=None, learning_rate=0.3, l2_regularization=1.0, min_samples_leaf=1,
+            max_bins=255, early_stopping=False, class_weight={0: 1.0, 1: spw}).fit(X, y)
+    t_fit = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    p_h = m.predict_proba(X)[:, 1]
+    t_pr = time.perf_counter() - t0
+    out["sklearn_hgb"] = {"fit_rounds_per_s": round(T / t_fit, 2), "predict_rows_per_s": round(n / t_pr, 0), "cores": os.cpu_count(),
+                          "train_auc": round(float(roc_auc_score(y, p_h)), 5)}
+    clf = XGBClassifier(n_estimators=T, max_depth=6, scale_pos_weight=spw, device=str(dev))
+    clf.fit(X[:1000], y[:1000])                       # library warm-up (module load, first-launch costs)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    clf.fit(X, y)
+    torch.cuda.synchronize()
+    t_fit = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    p = clf.predict_proba(X)[:, 1]
+    t_pr = time.perf_counter() - t0
+    out["b200"] = {"fit_rounds_per_s": round(T / t_fit, 2), "predict_rows_per_s": round(n / t_pr, 0),
+                   "what": "XGBClassifier.fit / predict_proba from host arrays (H2D, sketch, binning, D2H included)"}
+    out["parity"] = {"forest_equal": _forest_equal(clf.get_booster().forest, ref["flat"]),
+                     "max_dp": float(np.max(np.abs(p - p_ref))),
+                     "dauc": float(abs(roc_auc_score(y, p) - roc_auc_score(y, p_ref))), "train_auc": round(float(roc_auc_score(y, p_ref)), 5)}
+    return out
+
+
 def run_ours(args):
     import ctypes as C
 
@@ -218,21 +353,26 @@ def run_ours(args):
             _lib.check(lib.cb_trainer_level_split(tr.handle, level, st))
             acc_ms += a.value; red_ms += r_.value; n_launch += 1
             per_level.setdefault(level, []).append((int(rows.value), int(nb.value), round(a.value * 1e3, 1)))
-            # R*(F + 8 + 4) + nodes_built*F*B*16 ; the row-index term is 0 at the root
-            alg_bytes += rows.value * (N_FEAT + 8 + (0 if level == 0 else 4)) + nb.value * N_FEAT * 256 * 16
+            # R*(F + 8 + 4) + nodes_built*S*16 (S = total bins of the layout, not F*256);
+            # the row-index term is 0 at the root
+            alg_bytes += rows.value * (N_FEAT + 8 + (0 if level == 0 else 4)) + nb.value * S * 16
         _lib.check(lib.cb_trainer_round_end(tr.handle, st))
         tr.n_trees += 1
     torch.cuda.synchronize()
     lib.cb_trainer_enable_timing(tr.handle, 0)
     achieved = alg_bytes / (acc_ms / 1e3) / 1e9
-    traffic = None
+    traffic, traffic_src = None, None
     try:      # per-launch DRAM bytes of the same kernel from the committed ncu --set full capture
-        with open(os.path.join(ROOT, "profiles", "r01_roofline.json")) as fh:
+        rf = [f for f in ("r02_roofline.json", "r01_roofline.json") if os.path.exists(os.path.join(ROOT, "profiles", f))][0]
+        with open(os.path.join(ROOT, "profiles", rf)) as fh:
             traffic = int(json.load(fh)["dram_bytes_per_launch_mean"]) if world == 1 else None
+        traffic_src = f"profiles/{rf} (ncu --set full capture of the same command, committed)"
     except Exception:
         pass
     roofline = {"kernel": "hist_accum_cf_kernel" if cf_flag else "hist_accum_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
-                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src,
+                "peak_source": peak_src,
+                "frac_accum_plus_reduce": round(alg_bytes / ((acc_ms + red_ms) / 1e3) / 1e9 / peak, 4),
                 "avg_launch_ms": round(acc_ms / n_launch, 4), "launches_timed": n_launch,
                 "alg_bytes_per_launch": int(alg_bytes / n_launch), "hist_reduce_ms_per_launch": round(red_ms / n_launch, 4),
                 "hist_share_of_round": round((acc_ms + red_ms) / 3 / (ms / args.steps), 3),
@@ -262,6 +402,7 @@ def run_ours(args):
     cuts_cpu, nc_cpu, mv_cpu = cuts.cpu().numpy(), n_cuts.cpu().numpy(), min_vals.cpu().numpy()
     y_cpu = y.cpu().numpy()
     peer_mode = bool(tr.peer_mode)
+    fo_gpu = tr.forest_numpy() if bins_cpu is not None else None
     tr.close()
     del tr, bins, bins_cm
 
@@ -284,7 +425,7 @@ def run_ours(args):
             torch.distributed.all_reduce(t_fit, op=torch.distributed.ReduceOp.MAX)
         fo = clf.get_booster().forest
         d2h = sum(int(v.nbytes) for v in fo.values())
-        e2e = {"value": round(args.e2e_rounds / float(t_fit.item()), 2), "unit": "boosting rounds/s",
+        e2e = {"value": round(args.e2e_rounds / float(t_fit.item()), 2), "unit": "rounds/s",
                "h2d_bytes_per_step": int((Xn.nbytes + y_cpu.nbytes) / args.e2e_rounds),
                "d2h_bytes_per_step": int(d2h / args.e2e_rounds), "rounds": args.e2e_rounds,
                "fit_seconds": round(float(t_fit.item()), 3),
@@ -316,13 +457,42 @@ def run_ours(args):
         rows_s = args.score_rows / (ms_s / 1e3)
         sbytes = (s1 - s0) * (4 * N_FEAT + 4)
         visits = args.score_rows * SCORE_TREES * DEPTH
+        q8 = booster._device_q8(dev)
+        split = None
+        if q8 is not None:                     # per-kernel split of one pass: CUDA events around the two launches of every batch
+            evs = []
+            cuts_q, nc_q, words_q, depth_q, pbase_q = q8
+            ops.predict_q8(Xs, cuts_q, nc_q, words_q, depth_q, pbase_q, 0.0, SCORE_TREES, events=evs)
+            torch.cuda.synchronize()
+            t_codes = sum(e[0].elapsed_time(e[1]) for e in evs)
+            t_walk = sum(e[1].elapsed_time(e[2]) for e in evs)
+            nloc = s1 - s0
+            split = {"bin_rows_q8_kernel": {"ms": round(t_codes, 3), "alg_bytes": nloc * (4 * N_FEAT + N_FEAT),
+                                            "hbm_frac": round(nloc * 5 * N_FEAT / (t_codes / 1e3) / 1e9 / peak, 4)},
+                     "predict_q8_kernel": {"ms": round(t_walk, 3), "node_visits_per_s": round(nloc * SCORE_TREES * DEPTH / (t_walk / 1e3), 0),
+                                           "note": "reads the codes from L2 (batches of 512k rows); bound by shared-memory wavefronts and issue"}}
+        straffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "r02_predict_roofline.json")) as fh:
+                straffic = json.load(fh)
+        except Exception:
+            pass
         sc = {"metric": "scoring rows/s", "value": round(rows_s, 0), "ms_per_pass": round(ms_s, 3),
               "workload": f"{args.score_rows} rows x {N_FEAT}, {SCORE_TREES} trees depth {DEPTH} (configs[4])",
-              "roofline": {"kernel": "bin_pack_kernel + predict_q8_kernel" if booster._device_q8(dev) is not None else "predict_heap_kernel",
+              "roofline": {"kernel": "bin_rows_q8_kernel + predict_q8_kernel" if q8 is not None else "predict_heap_kernel",
                            "bound": "hbm (contract); binding resource is shared-memory lookups + ALU issue", "achieved": round(sbytes / (ms_s / 1e3) / 1e9, 1),
                            "peak": peak, "unit": "GB/s", "frac": round(sbytes / (ms_s / 1e3) / 1e9 / peak, 4),
-                           "traffic": None},
+                           "traffic": straffic, "per_kernel": split},
               "node_visits_per_s": round(visits / (ms_s / 1e3), 0)}
+        if rank == 0 and not args.no_cpu:      # parity on a sample of the benchmarked rows and forest
+            from oracle import oracle as O
+            ns_ = min(65536, s1 - s0)
+            fo_np = booster.forest
+            m_gpu = booster.predict_device(Xs[:ns_], output_margin=True).cpu().numpy()
+            m_cpu = O.predict_margin(Xs[:ns_].cpu().numpy(), fo_np["tree_offsets"], fo_np["left"], fo_np["right"], fo_np["split_index"],
+                                     fo_np["split_cond"], fo_np["default_left"], 0.0)
+            sc["parity"] = {"rows": ns_, "trees": SCORE_TREES, "margins_bitwise_equal": bool(np.array_equal(m_gpu.view(np.uint32), m_cpu.view(np.uint32))),
+                            "max_dp": float(np.max(np.abs(O.sigmoid(m_gpu) - O.sigmoid(m_cpu))))}
         if not args.no_e2e:
             Xsh = torch.empty(Xs.shape, dtype=torch.float32, pin_memory=True)
             Xsh.copy_(Xs)
@@ -368,33 +538,39 @@ def run_ours(args):
         del Xs
 
     # ---- CPU baseline: the oracle port on this box's host cores, same bins, bounded number of rounds
-    cpu = None
+    cpu = parity = hgb = c0 = None
     if rank == 0 and bins_cpu is not None:
         from oracle import oracle as O
+        O.set_threads(os.cpu_count() or 1)
         tp = O.TreeParams(eta=float(np.float32(ETA)), max_depth=DEPTH, sg=sg, sh=sh)
         margin = np.zeros(len(y_cpu), np.float32)
         bp = O.bin_ptr_of(nc_cpu)
-        O.train(bins_cpu, N_FEAT, bp, cuts_cpu, mv_cpu, y_cpu, None, spw, tp, 1, margin)
+        fo_a = O.train(bins_cpu, N_FEAT, bp, cuts_cpu, mv_cpu, y_cpu, None, spw, tp, 1, margin)
         t0 = time.perf_counter()
-        O.train(bins_cpu, N_FEAT, bp, cuts_cpu, mv_cpu, y_cpu, None, spw, tp, args.cpu_rounds, margin, tree_offset=1)
+        fo_b = O.train(bins_cpu, N_FEAT, bp, cuts_cpu, mv_cpu, y_cpu, None, spw, tp, args.cpu_rounds, margin, tree_offset=1)
         dt = time.perf_counter() - t0
-        cpu = {"value": round(args.cpu_rounds / dt, 3), "unit": "boosting rounds/s", "cores": O.num_threads(),
+        cpu = {"value": round(args.cpu_rounds / dt, 3), "unit": "rounds/s", "cores": O.num_threads(),
                "kind": "port", "sample": f"{args.cpu_rounds} rounds on the full {n_rows} x {N_FEAT} binned matrix "
                f"(rounds 2..{args.cpu_rounds + 1}), oracle/gbdt_oracle.c with OpenMP; reference xgboost unavailable on this box"}
+        # ---- parity ON THE BENCHMARKED CONFIGURATION: the GPU's first trees (same bins, same start margin 0) against
+        # the oracle's, bit for bit; then both forests on a held-out slice of fresh synthetic rows
+        K = args.cpu_rounds + 1
+        parity = _forest_parity(O, fo_gpu, [fo_a, fo_b], K, N_FEAT, dev, n_rows)
+        del bins_cpu
+        # ---- second CPU baseline (SURVEY 8d "always"): sklearn HistGradientBoostingClassifier, all cores, and config C0
+        if not args.no_hgb:
+            hgb = _hgb_baseline(n_rows, N_FEAT, DEPTH, dev)
+            c0 = _config_c0(O, dev)
 
     if rank == 0:
         line = {"metric": "boosting rounds/s", "value": round(rounds_per_s, 2), "unit": "rounds/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4),
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int64 fixed-point (f32 gradients, f64 gains)",
-                "data": "synthetic", "config": {"workload": WORKLOAD, "rows": n_rows, "features": N_FEAT, "max_bin": 256,
-                                                "max_depth": DEPTH, "rounds_timed": args.steps, "total_bins": S,
-                                                "l2_policy": "inputs larger than L2 (352 MB binned matrix vs 126 MB L2)" if world == 1 else
-                                                "binned shard may fit L2 at N>=4 (strong scaling of a 352 MB matrix)",
-                                                "parallelism": (f"rows sharded x{world}, " + (
-                                                    "per-level histograms summed over NVLink peer memory inside the split scan"
-                                                    if peer_mode else "NCCL allreduce of per-level histograms"))
-                                                if world > 1 else "single GPU"},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+                "data": "synthetic", "config": _config(n_rows, args.steps, args.warmup, world),
+                "detail": {"total_bins": S, "effective_bins_per_feature": 255,
+                           "exchange": ("NVLink peer memory inside the split scan" if peer_mode else "NCCL allreduce") if world > 1 else None},
+                "roofline": roofline, "cpu_baseline": cpu, "cpu_baseline_hgb": hgb, "parity": parity, "c0": c0,
+                "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clk.summary(), "scoring": scoring, "prep_ms": round(t_prep, 2), "train_auc_200k": auc}
         print(json.dumps(line), file=_OUT, flush=True)
     if world > 1:
@@ -403,8 +579,9 @@ def run_ours(args):
 
 
 def run_reference(args):
-    """The reference's CPU path for this metric: oracle port (xgboost is not installable here),
-    all host threads, one step = one boosting round on a bounded row sample of the workload."""
+    """The reference's CPU path for this metric: oracle port (xgboost is not installable here), all host threads
+    (torch.distributed.run exports OMP_NUM_THREADS=1: the thread count is set explicitly), one step = one boosting
+    round on the SAME rows x features x depth as our arm (no row sampling unless --ref-rows asks for it)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -413,7 +590,8 @@ def run_reference(args):
 
     from cobalt_smart_lender_ai_b200.synth import make_lending
     from oracle import oracle as O
-    n = min(args.rows, args.ref_rows)
+    O.set_threads(os.cpu_count() or 1)
+    n = min(args.rows, args.ref_rows) if args.ref_rows > 0 else args.rows
     dev = "cuda" if torch.cuda.is_available() else "cpu"
     X, y, _ = make_lending(n, N_FEAT, device=dev)
     X, y = X.cpu().numpy(), y.cpu().numpy()
@@ -432,13 +610,16 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     scale = n / args.rows
     val = args.steps / dt * scale
-    sample = (f"{n} of {args.rows} rows per step (value = measured rounds/s x {scale:.3f}, linear in rows); "
-              f"oracle/gbdt_oracle.c with OpenMP; reference xgboost unavailable on this box")
+    if n == args.rows:
+        sample = (f"every step is one round on the full {n} x {N_FEAT} binned matrix; oracle/gbdt_oracle.c with OpenMP on "
+                  f"{O.num_threads()} threads; reference xgboost unavailable on this box")
+    else:
+        sample = (f"{n} of {args.rows} rows per step (value = measured rounds/s x {scale:.3f}, linear in rows); "
+                  f"oracle/gbdt_oracle.c with OpenMP; reference xgboost unavailable on this box")
     line = {"impl": "reference", "metric": "boosting rounds/s", "value": round(val, 3), "unit": "rounds/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3 / scale, 2),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int64 fixed-point (f32 gradients, f64 gains)",
-            "data": "synthetic", "config": {"workload": WORKLOAD, "rows": args.rows, "features": N_FEAT, "max_bin": 256,
-                                            "max_depth": DEPTH},
+            "data": "synthetic", "config": _config(args.rows, args.steps, args.warmup, args.gpus),
             "cpu_baseline": {"value": round(val, 3), "unit": "rounds/s", "cores": O.num_threads(), "kind": "port", "sample": sample},
             "e2e": {"value": round(val, 3), "unit": "rounds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "raw_rounds_per_s_on_sample": round(args.steps / dt, 3), "prep_seconds": round(t_prep, 2)}
@@ -469,10 +650,11 @@ def main():
     ap.add_argument("--score-steps", type=int, default=3)
     ap.add_argument("--shap-rows", type=int, default=4096, help="rows explained with TreeSHAP in the scoring leg (0: skip)")
     ap.add_argument("--cpu-rounds", type=int, default=8)
-    ap.add_argument("--ref-rows", type=int, default=550_000)
+    ap.add_argument("--ref-rows", type=int, default=0, help="reference arm: rows per step (0 = the full --rows, the default)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-scoring", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-hgb", action="store_true", help="skip the sklearn HistGradientBoosting baseline and config C0")
     args = ap.parse_args()
     if args.depth != DEPTH or args.rows != N_ROWS:
         DEPTH = args.depth

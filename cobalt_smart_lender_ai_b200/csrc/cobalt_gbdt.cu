@@ -278,6 +278,15 @@ static int noalloc_scratch(FeatBest** out) {
   CB_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= kMaxDev) return fail(CB_ERR_UNSUPPORTED, "cb_split_scan_noalloc: device index %d not supported", dev);
   std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev]) {
+    // a cudaDeviceReset() since the set-up leaves a stale address behind: ask the driver whether it still is device
+    // memory of this GPU (a query, not an allocation) and look the symbol up again if not
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, ptrs[dev]) != cudaSuccess || at.type != cudaMemoryTypeDevice || at.device != dev) {
+      cudaGetLastError();
+      ptrs[dev] = nullptr;
+    }
+  }
   if (!ptrs[dev]) {
     FeatBest* p = nullptr;
     cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_feat_best);
@@ -949,8 +958,8 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   const int n = (int)t->cfg.n_rows;
   const int n_groups = ceil_div(t->n_part_tiles, kTileGroup);
   const int fx = t->pc.world > 1 ? t->pc.f1 - t->pc.f0 : t->cfg.n_features;   // peer mode: this rank's feature slice
-  if (fx > 0) {
-    scan_level_fused_kernel<<<dim3(fx, ln), 128, 0, s>>>(
+  {                                         // a rank whose slice is empty still needs the kernel's housekeeping CTA
+    scan_level_fused_kernel<<<dim3(fx > 0 ? fx : 1, ln), 128, 0, s>>>(
         t->level_buf, t->pool, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S, t->st, level, t->na, t->cfg.tree, t->fmask,
         t->feat_best, level == 0 ? t->level_buf + t->S2 : nullptr, t->st, t->group_cnt, n_groups, t->pc);
     t->launches += 1;

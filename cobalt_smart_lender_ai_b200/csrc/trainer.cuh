@@ -159,6 +159,7 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
     for (int k = threadIdx.x; k < n_groups; k += blockDim.x) group_cnt[k] = 0;
   if (i >= st->lvl_count[level]) return;
   const int feat = (pc.world > 1 ? pc.f0 : 0) + (int)blockIdx.x;
+  const bool no_feature = pc.world > 1 && feat >= pc.f1;     // empty slice (world > n_features): housekeeping only
   const int nid = st->lvl_first[level] + i;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   long long Gt, Ht;
@@ -173,6 +174,7 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
   } else {
     Gt = na.G[nid]; Ht = na.H[nid];
   }
+  if (no_feature) return;
   do {
   if (feature_mask && !feature_mask[(size_t)st->tree_index * f + feat]) {
     if (tid == 0) {

@@ -245,7 +245,7 @@ def predict_q8_plan(n_features: int, depth: int) -> tuple[int, int]:
 
 def predict_q8(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, forest: torch.Tensor, depth: int,
                plane_base: int, base_margin: float, n_trees: int, want_margin: bool = False, want_proba: bool = True,
-               batch_rows: int = 1 << 19):
+               batch_rows: int = 1 << 19, events: list | None = None):
     """K8 on quantised inputs: K2 against the forest's threshold table, then the byte-tile walk.  Rows go through
     in batches so that the code matrix (80 MB per batch) is still in L2 when the walk reads it."""
     _need_cuda(X, cuts, n_cuts, forest)
@@ -258,10 +258,18 @@ def predict_q8(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, forest
     codes = torch.empty((min(n, batch_rows), ldc), dtype=torch.uint8, device=X.device)
     for r0 in range(0, n, batch_rows):
         r1 = min(n, r0 + batch_rows)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if events is not None else None
+        if ev:
+            ev[0].record()
         check(lib.cb_bin_rows_u8(_ptr(X[r0:r1]), r1 - r0, f, _ld(X), _ptr(cuts), _ptr(n_cuts), _ptr(codes), ldc, _stream()))
+        if ev:
+            ev[1].record()
         check(lib.cb_predict_q8(_ptr(codes), r1 - r0, f, ldc, _ptr(forest), int(n_trees), depth, float(base_margin),
                                 int(plane_base), _ptr(m[r0:r1]) if m is not None else None,
                                 _ptr(p[r0:r1]) if p is not None else None, _stream()))
+        if ev:
+            ev[2].record()
+            events.append(ev)
     return m, p
 
 

@@ -3,10 +3,10 @@
 cb_split_scan_noalloc is the split-gain scan for callers that cannot hand the library a workspace --
 for instance a scoring/training service that reserves all of its device memory when it starts and must
 never call cudaMalloc afterwards, or a binding that can pass nothing but its own input and output
-buffers.  Its scratch is a fixed array inside the library, so the test checks three things through the
-C ABI: it returns exactly what cb_split_scan returns, it keeps doing so on a second call that uses
-fewer features than the first (left-over records must not leak), and it refuses inputs larger than its
-built-in scratch."""
+buffers.  Its scratch is a fixed array inside the library, so the test checks these things through the
+C ABI: it returns exactly what cb_split_scan returns AND what the CPU oracle's scan (R6/R7) returns, it
+keeps doing so on a second call that uses fewer features than the first (left-over records must not
+leak), and it refuses inputs larger than its built-in scratch."""
 import ctypes as C
 
 import numpy as np
@@ -66,6 +66,13 @@ def test_noalloc_split_scan_matches_workspace_version_twice_in_a_row():
             assert got[k] == want[k], k
         for k in ("loss_chg", "threshold"):            # bit-exact, like every other split test
             assert np.float32(got[k]).view(np.uint32) == np.float32(want[k]).view(np.uint32), k
+        # ... and against the oracle itself, not only against the sibling entry point
+        otp = O.TreeParams(eta=float(np.float32(0.3)), max_depth=6, sg=14, sh=16)
+        ref = O.scan(h, bp, cuts, mv, int(tot[0]), int(tot[1]), otp, feature_mask=mask)
+        for k in ("feature", "split_bin", "default_left", "GL", "HL", "GR", "HR"):
+            assert got[k] == ref[k], k
+        for k in ("loss_chg", "threshold"):
+            assert np.float32(got[k]).view(np.uint32) == np.float32(ref[k]).view(np.uint32), k
 
 
 def test_noalloc_split_scan_rejects_oversized_input():
