@@ -42,13 +42,13 @@ class TrainConfig(C.Structure):
     _fields_ = [("n_rows", C.c_int64), ("ldb", C.c_int64), ("row_offset", C.c_int64), ("n_features", C.c_int32),
                 ("total_bins", C.c_int32), ("max_trees", C.c_int32), ("world_size", C.c_int32),
                 ("tree", TreeParams), ("scale_pos_weight", C.c_float), ("keep_thresh", C.c_uint32),
-                ("seed", C.c_uint32), ("blocked", C.c_int32)]
+                ("seed", C.c_uint32), ("blocked", C.c_int32), ("n_groups", C.c_int32)]
 
 
 class TrainBuffers(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in (
         "bins", "y", "weight", "margin", "bin_ptr", "cuts", "min_vals", "pos_feature", "bins_cm", "left", "right", "parent", "split_index",
-        "split_bin", "split_cond", "default_left", "base_weight", "loss_chg", "sum_hess", "n_nodes")]
+        "split_bin", "split_cond", "default_left", "base_weight", "loss_chg", "sum_hess", "n_nodes", "grp_ptr", "grp_feat")]
 
 
 def sources() -> list[str]:
@@ -102,8 +102,9 @@ _SIGS = {
     "cb_device_info": (C.c_int, [C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "cb_sketch_workspace_bytes": (C.c_int, [_I64, _I, C.POINTER(_SZ)]),
     "cb_sketch_cuts": (C.c_int, [_VP, _I64, _I, _I64, _I, _VP, _VP, _VP, _VP, _SZ, _VP]),
-    "cb_plan_layout": (C.c_int, [_VP, _I, _I64, _VP, C.POINTER(C.c_int32)]),
-    "cb_bin_pack_u8": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _VP, _VP, _I64, _I, _VP]),
+    "cb_onehot_pair_counts": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _I, _VP, _VP, _VP]),
+    "cb_plan_layout": (C.c_int, [_VP, _I, _VP, _VP, _I, _I64, _VP, C.POINTER(C.c_int32)]),
+    "cb_bin_pack_u8": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _I, _VP]),
     "cb_bin_transpose_u8": (C.c_int, [_VP, _I64, _I64, _I, _VP, _VP]),
     "cb_grad_logistic_q": (C.c_int, [_VP, _VP, _VP, _I64, _F, _I, _I, _U32, _U32, _U32, _I64, _VP, _VP, _VP]),
     "cb_sigmoid": (C.c_int, [_VP, _I64, _VP, _VP]),

@@ -26,6 +26,25 @@ int device_info(DeviceInfo* out) {
 
 static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
+// Launch with programmatic stream serialisation (common.cuh pdl_enter): the kernel may be scheduled while its
+// predecessor in the stream is still draining; it blocks in griddepcontrol.wait until that one has completed.
+// COBALT_PDL=0 (read once) launches plainly, for A/B timing.
+static bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("COBALT_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
+template <typename... P, typename... A>
+static inline cudaError_t launch_dep(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, A&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof cfg);
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<P>(std::forward<A>(args))...);
+}
+
 // shared-memory budget of hist_accum in histogram slots (8 bytes per slot)
 static inline int hist_budget_slots(const DeviceInfo& di) { return (di.smem_optin - 2048) / 8; }
 static inline int hist_tiles_bound(int S, int budget) {
@@ -72,8 +91,26 @@ int cb_device_info(int* sm_count, int* smem_optin_bytes) {
 }
 
 // ---------------------------------------------------------------------------- K2
-int cb_plan_layout(const int32_t* n_cuts_host, int f, int64_t ldb, int32_t* pos_feature_host, int32_t* conflict_free) {
-  if (!n_cuts_host || !pos_feature_host || f <= 0 || ldb < f || (ldb & 3))
+int cb_onehot_pair_counts(const float* X, int64_t n, int f, int64_t ldx, const float* cuts, const int32_t* cand, int n_cand,
+                          uint64_t* pair, uint64_t* miss, void* stream) {
+  if (!X || !cuts || !cand || !pair || !miss || n < 0 || f <= 0 || ldx < f || n_cand < 1 || n_cand > 64)
+    return fail(CB_ERR_INVALID, "cb_onehot_pair_counts: bad arguments (1..64 candidates)");
+  if (n == 0) return CB_OK;
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  const int grid = (int)std::min<int64_t>(ceil_div(n, 256), (int64_t)di.sm_count * 4);
+  onehot_pair_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(X, n, ldx, cuts, cand, n_cand,
+                                                            reinterpret_cast<unsigned long long*>(pair),
+                                                            reinterpret_cast<unsigned long long*>(miss));
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+int cb_plan_layout(const int32_t* n_cuts_host, int f, const int32_t* grp_ptr_host, const int32_t* grp_feat_host, int n_groups,
+                   int64_t ldb, int32_t* pos_feature_host, int32_t* conflict_free) {
+  if (!n_cuts_host || !pos_feature_host || f <= 0 || ldb <= 0 || (ldb & 3) || n_groups < 0 ||
+      (n_groups > 0 && (!grp_ptr_host || !grp_feat_host)))
     return fail(CB_ERR_INVALID, "cb_plan_layout: bad arguments");
   DeviceInfo di;
   int rc = device_info(&di);
@@ -83,10 +120,18 @@ int cb_plan_layout(const int32_t* n_cuts_host, int f, int64_t ldb, int32_t* pos_
     if (n_cuts_host[i] < 1 || n_cuts_host[i] > CB_MAX_BINS) return fail(CB_ERR_INVALID, "cb_plan_layout: n_cuts[%d] out of range", i);
     bp[i + 1] = bp[i] + n_cuts_host[i];
   }
-  plan_positions(n_cuts_host, f, ldb, pos_feature_host);
+  GroupTable gt;
+  gt.n_groups = n_groups; gt.ptr = grp_ptr_host; gt.feat = grp_feat_host;
+  std::vector<int> group_of;
+  if (!check_groups(n_cuts_host, f, gt, &group_of))
+    return fail(CB_ERR_INVALID, "cb_plan_layout: a group holds a feature twice, out of range, or with other than 2 bins");
+  if (count_columns(f, gt) > ldb) return fail(CB_ERR_INVALID, "cb_plan_layout: ldb %lld < %d columns", (long long)ldb, count_columns(f, gt));
+  bool ok = plan_positions(n_cuts_host, f, gt, ldb, pos_feature_host);
   CfHostTables tb;
-  const bool ok = build_cf_tables(bp.data(), pos_feature_host, f, ldb, hist_budget_slots(di) * 8, &tb);
-  if (!ok) {                       // does not fit one shared-memory image: natural column order, tiled kernel
+  ok = ok && build_cf_tables(bp.data(), pos_feature_host, f, gt, ldb, hist_budget_slots(di) * 8, &tb);
+  if (!ok) {                       // does not fit one shared-memory image: natural column order, tiled kernel (no groups)
+    if (n_groups > 0) return fail(CB_ERR_UNSUPPORTED, "cb_plan_layout: grouped columns need the conflict-free layout, which does not fit; plan again without groups");
+    if (ldb < f) return fail(CB_ERR_INVALID, "cb_plan_layout: ldb < n_features");
     for (int64_t p = 0; p < ldb; ++p) pos_feature_host[p] = p < f ? (int32_t)p : -1;
   }
   if (conflict_free) *conflict_free = ok ? 1 : 0;
@@ -94,14 +139,16 @@ int cb_plan_layout(const int32_t* n_cuts_host, int f, int64_t ldb, int32_t* pos_
 }
 
 int cb_bin_pack_u8(const float* X, int64_t n, int f, int64_t ldx, const float* cuts, const int32_t* n_cuts,
-                   const int32_t* pos_feature, uint8_t* bins, int64_t ldb, int blocked, void* stream) {
-  if (!X || !cuts || !n_cuts || !bins || n < 0 || f <= 0 || ldx < f || ldb < f || (ldb & 3))
-    return fail(CB_ERR_INVALID, "cb_bin_pack_u8: bad arguments (ldb must be a multiple of 4 and >= n_features)");
+                   const int32_t* pos_feature, const int32_t* grp_ptr, const int32_t* grp_feat, uint8_t* bins, int64_t ldb,
+                   int blocked, void* stream) {
+  if (!X || !cuts || !n_cuts || !bins || n < 0 || f <= 0 || ldx < f || ldb <= 0 || (ldb & 3) || (!pos_feature && ldb < f) ||
+      ((grp_ptr == nullptr) != (grp_feat == nullptr)))
+    return fail(CB_ERR_INVALID, "cb_bin_pack_u8: bad arguments (ldb must be a multiple of 4 and hold every column)");
   if (n == 0) return CB_OK;
   int wpr = (int)(ldb / 4);
   int64_t items = n * wpr;
-  bin_pack_kernel<<<ceil_div(items, 256), 256, 0, (cudaStream_t)stream>>>(X, n, f, ldx, cuts, n_cuts, pos_feature, bins, wpr,
-                                                                         make_view(bins, n, ldb, blocked));
+  bin_pack_kernel<<<ceil_div(items, 256), 256, 0, (cudaStream_t)stream>>>(X, n, f, ldx, cuts, n_cuts, pos_feature, grp_ptr, grp_feat,
+                                                                         bins, wpr, make_view(bins, n, ldb, blocked));
   CB_LAUNCH_CHECK();
   return CB_OK;
 }
@@ -631,7 +678,9 @@ struct cb_trainer_s {
   int32_t* cf_slot_of;
   int32_t* cf_fold_src;
   int32_t* cf_fold_dst;
-  int32_t* feat_pos;      // [f] byte position of a feature inside a binned row
+  int32_t* feat_pos;      // [f] byte position of a feature's column inside a binned row
+  int32_t* feat_code;     // [f] 0 = plain feature, m + 1 = member m of a group column (bin 1 <=> column code == m + 1)
+  bool grouped;
   int part_words;         // int32 words per partial histogram
   // peer mode (row-sharded training over NVLink peer memory)
   PeerCtx pc;
@@ -673,6 +722,7 @@ static int trainer_layout(const cb_train_config* cfg, const DeviceInfo& di, void
   int32_t* cf_fold_src = b.take<int32_t>((size_t)cf_words);
   int32_t* cf_fold_dst = b.take<int32_t>((size_t)cf_words);
   int32_t* feat_pos = b.take<int32_t>((size_t)cfg->n_features);
+  int32_t* feat_code = b.take<int32_t>((size_t)cfg->n_features);
   SymHeader** d_peers = b.take<SymHeader*>(kMaxRanks);
   int64_t** d_peer_lb = b.take<int64_t*>(kMaxRanks);
   if (bytes) *bytes = b.used();
@@ -683,7 +733,7 @@ static int trainer_layout(const cb_train_config* cfg, const DeviceInfo& di, void
     t->st = st; t->segs = segs; t->plan = plan; t->na = na; t->pool = pool; t->level_buf = level_buf;
     t->partials = partials; t->feat_best = feat_best;
     t->cf_lay = cf_lay; t->cf_slot_of = cf_slot_of; t->cf_fold_src = cf_fold_src; t->cf_fold_dst = cf_fold_dst;
-    t->feat_pos = feat_pos; t->part_words = part_words;
+    t->feat_pos = feat_pos; t->feat_code = feat_code; t->part_words = part_words;
     t->d_peers = d_peers; t->d_peer_lb = d_peer_lb;
   }
   return CB_OK;
@@ -692,8 +742,8 @@ static int trainer_layout(const cb_train_config* cfg, const DeviceInfo& di, void
 static int trainer_check_cfg(const cb_train_config* cfg) {
   if (!cfg) return fail(CB_ERR_INVALID, "trainer: null config");
   if (cfg->n_rows <= 0 || cfg->n_rows > 2147483647LL) return fail(CB_ERR_INVALID, "trainer: n_rows out of range");
-  if (cfg->n_features <= 0 || cfg->ldb < cfg->n_features || (cfg->ldb & 3))
-    return fail(CB_ERR_INVALID, "trainer: ldb must be a multiple of 4 and >= n_features");
+  if (cfg->n_features <= 0 || cfg->ldb <= 0 || (cfg->ldb & 3) || cfg->n_groups < 0 || (cfg->n_groups == 0 && cfg->ldb < cfg->n_features))
+    return fail(CB_ERR_INVALID, "trainer: ldb must be a multiple of 4 and hold every column");
   if (cfg->tree.max_depth < 1 || cfg->tree.max_depth > kMaxDepth)
     return fail(CB_ERR_UNSUPPORTED, "trainer: max_depth must be in [1, %d]", kMaxDepth);
   if (cfg->total_bins <= 0 || cfg->total_bins > cfg->n_features * CB_MAX_BINS)
@@ -757,23 +807,53 @@ int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, v
   // column placement -> conflict-free shared-memory tables (host side, one-off)
   {
     const int f = cfg->n_features;
-    std::vector<int32_t> bp((size_t)f + 1), pf((size_t)cfg->ldb), fp((size_t)f, -1);
+    std::vector<int32_t> bp((size_t)f + 1), pf((size_t)cfg->ldb), fp((size_t)f, -1), fc((size_t)f, 0);
     e = cudaMemcpy(bp.data(), buf->bin_ptr, sizeof(int32_t) * (f + 1), cudaMemcpyDeviceToHost);
     if (e == cudaSuccess && buf->pos_feature)
       e = cudaMemcpy(pf.data(), buf->pos_feature, sizeof(int32_t) * cfg->ldb, cudaMemcpyDeviceToHost);
+    const int ng = cfg->n_groups;
+    std::vector<int32_t> gptr((size_t)ng + 1, 0), gfeat;
+    if (ng < 0 || (ng > 0 && (!buf->grp_ptr || !buf->grp_feat || !buf->pos_feature))) {
+      delete t; return fail(CB_ERR_INVALID, "trainer: n_groups > 0 needs grp_ptr, grp_feat and pos_feature");
+    }
+    if (e == cudaSuccess && ng > 0) {
+      e = cudaMemcpy(gptr.data(), buf->grp_ptr, sizeof(int32_t) * (ng + 1), cudaMemcpyDeviceToHost);
+      if (e == cudaSuccess) {
+        if (gptr[0] != 0 || gptr[ng] < ng || gptr[ng] > f) { delete t; return fail(CB_ERR_INVALID, "trainer: grp_ptr is malformed"); }
+        gfeat.resize((size_t)gptr[ng]);
+        e = cudaMemcpy(gfeat.data(), buf->grp_feat, sizeof(int32_t) * gfeat.size(), cudaMemcpyDeviceToHost);
+      }
+    }
     if (e != cudaSuccess) { delete t; return fail(CB_ERR_CUDA, "cb_trainer_create: %s", cudaGetErrorString(e)); }
     if (!buf->pos_feature)
       for (int64_t p = 0; p < cfg->ldb; ++p) pf[p] = p < f ? (int32_t)p : -1;
     if (bp[f] != cfg->total_bins) { delete t; return fail(CB_ERR_INVALID, "trainer: total_bins does not match bin_ptr"); }
-    for (int64_t p = 0; p < cfg->ldb; ++p)
+    GroupTable gt;
+    gt.n_groups = ng; gt.ptr = gptr.data(); gt.feat = gfeat.data();
+    {
+      std::vector<int32_t> nc((size_t)f);
+      for (int i = 0; i < f; ++i) nc[i] = bp[i + 1] - bp[i];
+      std::vector<int> group_of;
+      if (!check_groups(nc.data(), f, gt, &group_of)) { delete t; return fail(CB_ERR_INVALID, "trainer: malformed feature groups"); }
+    }
+    for (int64_t p = 0; p < cfg->ldb; ++p) {
       if (pf[p] >= 0 && pf[p] < f) fp[pf[p]] = (int32_t)p;
+      else if (is_group_key(pf[p]) && group_of_key(pf[p]) < ng) {
+        const int g = group_of_key(pf[p]);
+        for (int k = gptr[g]; k < gptr[g + 1]; ++k) { fp[gfeat[k]] = (int32_t)p; fc[gfeat[k]] = k - gptr[g] + 1; }
+      }
+    }
     for (int i = 0; i < f; ++i)
       if (fp[i] < 0) { delete t; return fail(CB_ERR_INVALID, "trainer: pos_feature does not place feature %d", i); }
+    t->grouped = ng > 0;
     CfHostTables tb;
-    t->cf = build_cf_tables(bp.data(), pf.data(), f, cfg->ldb, budget * 8, &tb);
+    t->cf = build_cf_tables(bp.data(), pf.data(), f, gt, cfg->ldb, budget * 8, &tb);
     const bool multi = (cfg->ldb + 127) / 128 > 1;
     if (t->cf && multi && !cfg->blocked) t->cf = false;     // row-major rows wider than one block: tiled kernel
     if (!t->cf && multi && cfg->blocked) { delete t; return fail(CB_ERR_UNSUPPORTED, "trainer: block-major bins need a conflict-free layout"); }
+    if (!t->cf && ng > 0) { delete t; return fail(CB_ERR_UNSUPPORTED, "trainer: grouped columns need the conflict-free layout"); }
+    e = cudaMemcpy(t->feat_code, fc.data(), sizeof(int32_t) * f, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { delete t; return fail(CB_ERR_CUDA, "cb_trainer_create: %s", cudaGetErrorString(e)); }
     e = cudaMemcpy(t->feat_pos, fp.data(), sizeof(int32_t) * f, cudaMemcpyHostToDevice);
     if (t->cf && e == cudaSuccess) {
       t->cf_R = tb.lay.R; t->cf_smem = tb.lay.R * 32 * 8;
@@ -876,15 +956,15 @@ int cb_trainer_round_begin(cb_trainer* t, int tree_index, const uint8_t* feature
     t->launches += 1;
   }
   mark(t, s, "start");
-  CB_CUDA(cudaMemsetAsync(t->st->root_tot, 0, 2 * sizeof(long long), s));
   int g = (int)std::min<int64_t>(ceil_div(n, 256), (int64_t)t->di.sm_count * 8);
-  grad_kernel<<<g, 256, 0, s>>>(t->buf.margin, t->buf.y, t->buf.weight, n, t->cfg.scale_pos_weight,
-                                ldexpf(1.0f, t->cfg.tree.sg), ldexpf(1.0f, t->cfg.tree.sh), t->cfg.keep_thresh,
-                                t->cfg.seed, 0u, t->cfg.row_offset, t->gpair,
-                                reinterpret_cast<unsigned long long*>(t->st->root_tot), &t->st->tree_index);
+  // root_tot is zero here: init_state_kernel / the previous round's round_end_kernel cleared it
+  CB_CUDA(launch_dep(grad_kernel, dim3(g), dim3(256), 0, s, t->buf.margin, t->buf.y, t->buf.weight, n, t->cfg.scale_pos_weight,
+                     ldexpf(1.0f, t->cfg.tree.sg), ldexpf(1.0f, t->cfg.tree.sh), t->cfg.keep_thresh, t->cfg.seed, 0u,
+                     t->cfg.row_offset, t->gpair, reinterpret_cast<unsigned long long*>(t->st->root_tot),
+                     (const int*)&t->st->tree_index));
   mark(t, s, "grad");
-  round_init_kernel<<<ceil_div(t->max_nodes, 256), 256, 0, s>>>(t->st, t->na, tree_out(t), t->max_nodes, (int)n,
-                                                                t->plan, t->grid);
+  CB_CUDA(launch_dep(round_init_kernel, dim3(ceil_div(t->max_nodes, 256)), dim3(256), 0, s, t->st, t->na, tree_out(t),
+                     t->max_nodes, (int)n, t->plan, t->grid));
   mark(t, s, "round_init");
   CB_LAUNCH_CHECK();
   t->launches += 2;
@@ -896,28 +976,17 @@ int cb_trainer_level_hist(cb_trainer* t, int level, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   const int nb = level == 0 ? 1 : (1 << (level - 1));
   if (t->cf) {
-    const int gx = ceil_div(t->cf_R * 32 / 4, 256);
-    // z-slices per node: the partials are spread unevenly over the nodes (CTAs follow the rows), and the slice count
-    // is what bounds the longest chain of a big node's CTAs; empty slices of small nodes exit at once
-    int nz = std::max((2 * t->di.sm_count) / (gx * nb), 64 / nb);
-    nz = nz < 1 ? 1 : (nz > 16 ? 16 : nz);
-    if (nz > 1) CB_CUDA(cudaMemsetAsync(t->level_buf, 0, sizeof(int64_t) * (size_t)nb * t->S2, s));
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
     const BinsView bv = make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked);
-    if (t->identity)
-      hist_accum_cf_kernel<4, true><<<t->grid, 1024, kCfSmemBytes, s>>>(
-          t->buf.bins, bv.blocked ? t->cfg.n_rows : 0, bv.blocked ? bv.last_w : (int)t->cfg.ldb, t->gpair,
-          t->rows[t->cur], t->plan, t->cf_lay, t->cf_fold_src, t->cf_fold_dst, t->partials);
-    else
-      hist_accum_cf_kernel<4, false><<<t->grid, 1024, kCfSmemBytes, s>>>(
-          t->buf.bins, bv.blocked ? t->cfg.n_rows : 0, bv.blocked ? bv.last_w : (int)t->cfg.ldb, t->gpair,
-          t->rows[t->cur], t->plan, t->cf_lay, t->cf_fold_src, t->cf_fold_dst, t->partials);
-    if (t->timing) CB_CUDA(cudaEventRecord(t->ev[1], s));
-    mark(t, s, "hist_accum");
-    hist_reduce_cf_kernel<<<dim3(gx, nb, nz), 256, 0, s>>>(t->partials, t->plan, t->cf_R, t->S, t->cf_slot_of,
-                                                          t->level_buf);
-    mark(t, s, "hist_reduce");
-    if (t->timing) CB_CUDA(cudaEventRecord(t->ev[2], s));
+    auto kern = t->identity ? hist_accum_cf_kernel<4, true> : hist_accum_cf_kernel<4, false>;
+    CB_CUDA(launch_dep(kern, dim3(t->grid), dim3(1024), (size_t)kCfSmemBytes, s, t->buf.bins,
+                       (int64_t)(bv.blocked ? t->cfg.n_rows : 0), bv.blocked ? bv.last_w : (int)t->cfg.ldb, t->gpair,
+                       t->rows[t->cur], t->plan, t->cf_lay, t->cf_fold_src, t->cf_fold_dst, t->partials, t->cf_slot_of,
+                       t->S, t->level_buf, t->plan->done, &t->st->peer_timeout, t->st->root_tot,
+                       level == 0 ? t->level_buf + t->S2 : nullptr));
+    if (t->timing) { CB_CUDA(cudaEventRecord(t->ev[1], s)); CB_CUDA(cudaEventRecord(t->ev[2], s)); }
+    mark(t, s, "hist_accum+reduce");
+    t->launches += 1;
   } else {
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
     int rc = launch_hist_accum(t->buf.bins, t->cfg.ldb, reinterpret_cast<const int32_t*>(t->gpair), t->rows[t->cur],
@@ -927,14 +996,14 @@ int cb_trainer_level_hist(cb_trainer* t, int level, void* stream) {
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[1], s));
     hist_reduce_kernel<<<dim3(ceil_div(t->S, 256), nb), 256, 0, s>>>(t->partials, t->plan, t->S, t->level_buf);
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[2], s));
-  }
-  t->launches += 2;
-  if (level == 0) {
-    root_totals_kernel<<<1, 1, 0, s>>>(t->st, t->level_buf + t->S2);
-    t->launches += 1;
+    t->launches += 2;
+    if (level == 0) {
+      root_totals_kernel<<<1, 1, 0, s>>>(t->st, t->level_buf + t->S2);
+      t->launches += 1;
+    }
   }
   if (t->pc.world > 1) {                  // peers may now read this rank's level buffer
-    peer_signal_kernel<<<1, 32, 0, s>>>(t->pc, t->st, level, 0);
+    CB_CUDA(launch_dep(peer_signal_kernel, dim3(1), dim3(32), 0, s, t->pc, (const TreeState*)t->st, level, 0));
     t->launches += 1;
     mark(t, s, "signal");
   }
@@ -959,20 +1028,22 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   const int n_groups = ceil_div(t->n_part_tiles, kTileGroup);
   const int fx = t->pc.world > 1 ? t->pc.f1 - t->pc.f0 : t->cfg.n_features;   // peer mode: this rank's feature slice
   {                                         // a rank whose slice is empty still needs the kernel's housekeeping CTA
-    scan_level_fused_kernel<<<dim3(fx > 0 ? fx : 1, ln), 128, 0, s>>>(
-        t->level_buf, t->pool, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S, t->st, level, t->na, t->cfg.tree, t->fmask,
-        t->feat_best, level == 0 ? t->level_buf + t->S2 : nullptr, t->st, t->group_cnt, n_groups, t->pc);
+    CB_CUDA(launch_dep(scan_level_fused_kernel, dim3(fx > 0 ? fx : 1, ln), dim3(128), 0, s,
+                       t->level_buf, t->pool, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S, t->st, level, t->na, t->cfg.tree,
+                       t->fmask, t->feat_best, level == 0 ? t->level_buf + t->S2 : nullptr, t->st, t->group_cnt, n_groups, t->pc,
+                       t->grouped ? t->feat_code : nullptr));
     t->launches += 1;
   }
   mark(t, s, "scan");
   if (t->pc.world > 1) {
-    peer_publish_kernel<<<1, 256, 0, s>>>(t->pc, t->st, level, t->feat_best, t->cfg.n_features);
+    CB_CUDA(launch_dep(peer_publish_kernel, dim3(1), dim3(256), 0, s, t->pc, (const TreeState*)t->st, level,
+                       (const FeatBest*)t->feat_best, t->cfg.n_features));
     t->launches += 1;
     mark(t, s, "publish");
   }
   LevelCtx lc;
   lc.st = t->st; lc.level = level; lc.max_depth = D; lc.f = t->cfg.n_features; lc.feat_best = t->feat_best;
-  lc.p = t->cfg.tree; lc.na = t->na; lc.feat_pos = t->feat_pos; lc.pc = t->pc;
+  lc.p = t->cfg.tree; lc.na = t->na; lc.feat_pos = t->feat_pos; lc.feat_code = t->grouped ? t->feat_code : nullptr; lc.pc = t->pc;
   const BinsView view = make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked);
   const uint32_t* rin = t->rows[t->cur];
   const int ident = t->identity ? 1 : 0;
@@ -980,21 +1051,21 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
     uint32_t* rout = t->rows[t->cur ^ 1];
     const int pgrid = std::min(t->n_part_tiles, t->res_flags - 1) + 1;
     const int sgrid = std::min(t->n_part_tiles, t->res_scatter - 1) + 1;
-    part_level_flags_kernel<<<pgrid, 256, 0, s>>>(view, t->buf.bins_cm, rin, ident, n, t->n_part_tiles, lc, t->st,
-                                                                t->buf.cuts, t->buf.min_vals, tree_out(t), t->segs,
-                                                                t->flag_bits, t->tile_cnt, t->group_cnt);
+    CB_CUDA(launch_dep(part_level_flags_kernel, dim3(pgrid), dim3(256), 0, s, view, t->buf.bins_cm, rin, ident, n,
+                       t->n_part_tiles, lc, t->st, t->buf.cuts, t->buf.min_vals, tree_out(t), t->segs, t->flag_bits,
+                       t->tile_cnt, t->group_cnt));
     mark(t, s, "flags+finish");
-    part_level_scatter_kernel<<<sgrid, 256, 0, s>>>(rin, ident, n, t->n_part_tiles, t->segs, t->flag_bits,
-                                                                  t->tile_cnt, t->group_cnt, rout, t->buf.margin, t->st,
-                                                                  level, D, t->na, t->plan, t->grid,
-                                                                  t->cfg.world_size > 1 ? 1 : 0);
+    CB_CUDA(launch_dep(part_level_scatter_kernel, dim3(sgrid), dim3(256), 0, s, rin, ident, n, t->n_part_tiles,
+                       (const LevelSegs*)t->segs, (const uint32_t*)t->flag_bits, (const int*)t->tile_cnt,
+                       (const int*)t->group_cnt, rout, t->buf.margin, t->st, level, D, t->na, t->plan, t->grid,
+                       t->cfg.world_size > 1 ? 1 : 0));
     mark(t, s, "scatter+plan");
     t->cur ^= 1; t->identity = false;
     t->launches += 2;
   } else {
     const int nblk = ceil_div(n, 1024);
-    final_apply_kernel<<<std::min(nblk, t->res_final - 1) + 1, 256, 0, s>>>(view, t->buf.bins_cm, rin, ident, n, nblk, lc, t->st, t->buf.cuts,
-                                                t->buf.min_vals, tree_out(t), t->segs, t->buf.margin);
+    CB_CUDA(launch_dep(final_apply_kernel, dim3(std::min(nblk, t->res_final - 1) + 1), dim3(256), 0, s, view, t->buf.bins_cm,
+                       rin, ident, n, nblk, lc, t->st, t->buf.cuts, t->buf.min_vals, tree_out(t), t->segs, t->buf.margin));
     mark(t, s, "final_apply");
     t->launches += 1;
   }
@@ -1004,7 +1075,7 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
 
 int cb_trainer_round_end(cb_trainer* t, void* stream) {
   if (!t) return fail(CB_ERR_INVALID, "trainer: null handle");
-  round_end_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(t->st, t->buf.n_nodes);
+  CB_CUDA(launch_dep(round_end_kernel, dim3(1), dim3(256), 0, (cudaStream_t)stream, t->st, t->buf.n_nodes));
   CB_LAUNCH_CHECK();
   t->launches += 1;
   return CB_OK;

@@ -133,6 +133,15 @@ struct LevelTraceScope {
 #define CB_LEVEL_TRACE_SCOPE(kernel)
 #endif
 
+// ---- programmatic dependent launch: every kernel of a boosting round is launched with the stream-serialisation
+// attribute (cobalt_gbdt.cu launch_dep) and starts with pdl_enter(): it lets ITS successor be scheduled as soon as all
+// of this grid's CTAs run, then blocks until its predecessor has completed and flushed its memory.  The launch gap and
+// the scheduling ramp of kernel k + 1 overlap the tail of kernel k; ordering is unchanged (wait = full completion).
+__device__ __forceinline__ void pdl_enter() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 constexpr int kChunkRows = 16352;  // rows per int32 partial histogram: 16352 * 2^17 < 2^31
 constexpr int kPartTile = 1024;    // positions per partition tile
 

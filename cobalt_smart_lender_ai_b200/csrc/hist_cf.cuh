@@ -38,37 +38,85 @@ struct CfHostTables {
   std::vector<int32_t> fold_src, fold_dst;
 };
 
-// column positions: features sorted by descending bin count, dealt round robin to the words of a block
-inline void plan_positions(const int32_t* n_cuts, int f, int64_t ldb, int32_t* pos_feature) {
-  std::vector<int> order(f);
-  for (int i = 0; i < f; ++i) order[i] = i;
-  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return n_cuts[a] > n_cuts[b]; });
+// Storage columns.  A binned row holds one byte per COLUMN; a column is either a plain feature or a GROUP of
+// mutually exclusive 2-bin features (one-hot dummies, reference src/data_preprocessing/feature_engineering.py:142-147)
+// packed as one code: 0 = no member set, m + 1 = member m set.  pos_feature[p] names the column of byte p:
+// >= 0 a plain feature, -1 padding, <= -2 group g = -2 - value.  A group of k members is one histogram of k + 1
+// bins: one pair of shared-memory atomics per row instead of k pairs.
+struct GroupTable {                    // host
+  int n_groups = 0;
+  const int32_t* ptr = nullptr;        // [n_groups + 1]
+  const int32_t* feat = nullptr;       // members, group after group; the position inside a group + 1 is the code
+  int size(int g) const { return ptr[g + 1] - ptr[g]; }
+};
+inline int group_key(int g) { return -2 - g; }
+inline bool is_group_key(int v) { return v <= -2; }
+inline int group_of_key(int v) { return -2 - v; }
+
+// false when the groups are malformed (a feature twice, out of range, or not a 2-bin feature)
+inline bool check_groups(const int32_t* n_cuts, int f, const GroupTable& gt, std::vector<int>* group_of) {
+  group_of->assign(f, -1);
+  for (int g = 0; g < gt.n_groups; ++g) {
+    if (gt.size(g) < 1 || gt.size(g) > 254) return false;
+    for (int k = gt.ptr[g]; k < gt.ptr[g + 1]; ++k) {
+      const int ft = gt.feat[k];
+      if (ft < 0 || ft >= f || (*group_of)[ft] >= 0 || n_cuts[ft] != 2) return false;
+      (*group_of)[ft] = g;
+    }
+  }
+  return true;
+}
+
+inline int count_columns(int f, const GroupTable& gt) {
+  int members = 0;
+  for (int g = 0; g < gt.n_groups; ++g) members += gt.size(g);
+  return f - members + gt.n_groups;
+}
+
+// column positions: columns sorted by descending bin count, dealt round robin to the words of a block
+inline bool plan_positions(const int32_t* n_cuts, int f, const GroupTable& gt, int64_t ldb, int32_t* pos_feature) {
+  std::vector<int> group_of;
+  if (!check_groups(n_cuts, f, gt, &group_of)) return false;
+  std::vector<int> order, nb;
+  for (int i = 0; i < f; ++i)
+    if (group_of[i] < 0) { order.push_back(i); nb.push_back(n_cuts[i]); }
+  for (int g = 0; g < gt.n_groups; ++g) { order.push_back(group_key(g)); nb.push_back(gt.size(g) + 1); }
+  const int nc = (int)order.size();
+  std::vector<int> idx(nc);
+  for (int i = 0; i < nc; ++i) idx[i] = i;
+  std::stable_sort(idx.begin(), idx.end(), [&](int a, int b) { return nb[a] > nb[b]; });
   for (int64_t p = 0; p < ldb; ++p) pos_feature[p] = -1;
-  const int W = (f + 3) / 4;
+  const int W = (nc + 3) / 4;
+  if ((int64_t)W * 4 > ldb) return false;
   int next = 0;
   for (int k = 0; k * 32 < W; ++k) {
     const int wk = std::min(32, W - 32 * k);
-    const int take = std::min(f - next, 4 * wk);
+    const int take = std::min(nc - next, 4 * wk);
     for (int r = 0; r < take; ++r) {
       const int word = r % wk, j = r / wk;
-      pos_feature[(32 * k + word) * 4 + j] = order[next + r];
+      pos_feature[(32 * k + word) * 4 + j] = order[idx[next + r]];
     }
     next += take;
   }
+  return true;
 }
 
 // builds the shared-memory tables for a given column placement; false when it does not fit
-inline bool build_cf_tables(const int32_t* bin_ptr, const int32_t* pos_feature, int f, int64_t ldb, int budget_bytes,
-                            CfHostTables* out) {
-  const int W = (f + 3) / 4;
-  if ((int64_t)W * 4 > ldb) return false;
+inline bool build_cf_tables(const int32_t* bin_ptr, const int32_t* pos_feature, int f, const GroupTable& gt, int64_t ldb,
+                            int budget_bytes, CfHostTables* out) {
+  int last = -1;                                          // last byte position in use
+  for (int64_t p = 0; p < ldb; ++p)
+    if (pos_feature[p] != -1) last = (int)p;
+  const int W = last / 4 + 1;
+  if (last < 0 || (int64_t)W * 4 > ldb) return false;
   const int nb = (W + 31) / 32;
   if (nb > kCfMaxBlocks) return false;
+  auto col_bins = [&](int col) { return is_group_key(col) ? gt.size(group_of_key(col)) + 1 : bin_ptr[col + 1] - bin_ptr[col]; };
   CfLayout& L = out->lay;
   memset(&L, 0, sizeof L);
   L.n_blocks = nb;
   int bank_rows[32] = {0};
-  struct Rec { int k, l, j, rowbase, feat; };
+  struct Rec { int k, l, j, rowbase, col; };
   std::vector<Rec> recs;
   for (int k = 0; k < nb; ++k) {
     const int wk = std::min(32, W - 32 * k);
@@ -79,13 +127,13 @@ inline bool build_cf_tables(const int32_t* bin_ptr, const int32_t* pos_feature, 
       if (l >= ck * wk) continue;
       const int word = 32 * k + l % wk;
       for (int j = 0; j < 4; ++j) {
-        const int feat = pos_feature[word * 4 + j];
-        if (feat < 0) continue;
-        if (feat >= f) return false;
-        const int nbins = bin_ptr[feat + 1] - bin_ptr[feat];
+        const int col = pos_feature[word * 4 + j];
+        if (col == -1) continue;
+        if (col >= f || (is_group_key(col) && group_of_key(col) >= gt.n_groups)) return false;
+        const int nbins = col_bins(col);
         L.a0[k][l][j] = bank_rows[l] * 32 + l;
         L.nbj[k][l][j] = nbins;
-        recs.push_back(Rec{k, l, j, bank_rows[l], feat});
+        recs.push_back(Rec{k, l, j, bank_rows[l], col});
         bank_rows[l] += nbins + 1;                      // + the row that takes missing values
       }
     }
@@ -101,11 +149,19 @@ inline bool build_cf_tables(const int32_t* bin_ptr, const int32_t* pos_feature, 
   if (R > 896 || (int64_t)2 * 28672 * 4 > budget_bytes + 2048) return false;   // kCfMaxRows, kCfSmemBytes
   out->slot_of.assign((size_t)R * 32, -1);
   out->fold_src.clear(); out->fold_dst.clear();
+  // global slot of code b of a column: a plain feature's bin b; for a group, code m + 1 is bin 1 of member m
+  // (code 0, "no member set", has no slot: every member's bin 0 is node total - bin 1, derived in the split scan)
+  auto slot_of_code = [&](int col, int b) {
+    if (!is_group_key(col)) return bin_ptr[col] + b;
+    if (b == 0) return -1;
+    const int g = group_of_key(col);
+    return bin_ptr[gt.feat[gt.ptr[g] + b - 1]] + 1;
+  };
   for (const Rec& r : recs) {
     const int wk = L.wk[r.k];
-    const int nbins = bin_ptr[r.feat + 1] - bin_ptr[r.feat];
+    const int nbins = col_bins(r.col);
     if (r.l < wk) {
-      for (int b = 0; b < nbins; ++b) out->slot_of[(size_t)(r.rowbase + b) * 32 + r.l] = bin_ptr[r.feat] + b;
+      for (int b = 0; b < nbins; ++b) out->slot_of[(size_t)(r.rowbase + b) * 32 + r.l] = slot_of_code(r.col, b);
     } else {
       const int l0 = r.l % wk;
       const int dst0 = L.a0[r.k][l0][r.j];
@@ -116,12 +172,21 @@ inline bool build_cf_tables(const int32_t* bin_ptr, const int32_t* pos_feature, 
     }
   }
   L.n_fold = (int)out->fold_src.size();
-  // every feature must have been placed exactly once
-  std::vector<int> seen(f, 0);
-  for (int64_t p = 0; p < (int64_t)W * 4; ++p)
-    if (pos_feature[p] >= 0) seen[pos_feature[p]]++;
+  // every column must have been placed exactly once (grouped features through their group only)
+  std::vector<int> group_of;
+  std::vector<int32_t> nc(f);
+  for (int i = 0; i < f; ++i) nc[i] = bin_ptr[i + 1] - bin_ptr[i];
+  if (!check_groups(nc.data(), f, gt, &group_of)) return false;
+  std::vector<int> seen_f(f, 0), seen_g(gt.n_groups, 0);
+  for (int64_t p = 0; p < (int64_t)W * 4; ++p) {
+    const int col = pos_feature[p];
+    if (col >= 0) seen_f[col]++;
+    else if (is_group_key(col)) seen_g[group_of_key(col)]++;
+  }
   for (int i = 0; i < f; ++i)
-    if (seen[i] != 1) return false;
+    if (seen_f[i] != (group_of[i] < 0 ? 1 : 0)) return false;
+  for (int g = 0; g < gt.n_groups; ++g)
+    if (seen_g[g] != 1) return false;
   return true;
 }
 
@@ -154,17 +219,35 @@ __device__ __forceinline__ void cf_add_byte_at(uint32_t word, uint32_t nb, uint3
       : "memory");
 }
 
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
 // 1024 threads = 32 warps; warp w takes row groups w, w + 32, ... of the CTA's slice, one column
 // block after the other (each block is its own contiguous array: block-major storage).
-// Partials are written in shared-memory order ([2][R*32] int32), un-permuted by the reduce kernel.
+//
+// The reduction to the int64 level buffer happens in the same launch.  The grid never exceeds one CTA per SM, so
+// all of a node's CTAs are resident together and may wait for each other:
+//   * a node that one CTA covers in one chunk goes from shared memory straight to the level buffer;
+//   * otherwise every CTA stores its int32 partials (shared-memory order, coalesced), the node's CTAs meet at a
+//     counter, and then each of them sums ITS slice of the words over all of the node's partials
+//     (int32 -> int64, un-permuted through slot_of).
+// No second kernel, no zeroed buffer, no atomics on the level buffer: every slot is written exactly once.
 template <int UNROLL, bool IDENTITY>
 __global__ void __launch_bounds__(1024, 1)
 hist_accum_cf_kernel(const uint8_t* __restrict__ bins, int64_t n_rows, int last_w, const int2* __restrict__ gpair,
                      const uint32_t* __restrict__ row_idx, const HistPlan* __restrict__ plan,
                      const CfLayout* __restrict__ lay, const int32_t* __restrict__ fold_src,
-                     const int32_t* __restrict__ fold_dst, int32_t* __restrict__ partials) {
+                     const int32_t* __restrict__ fold_dst, int32_t* __restrict__ partials,
+                     const int32_t* __restrict__ slot_of, int S, int64_t* __restrict__ level_buf,
+                     unsigned int* __restrict__ done, unsigned int* __restrict__ wait_timeout,
+                     const long long* __restrict__ root_tot, int64_t* __restrict__ root_tail) {
   CB_LEVEL_TRACE_SCOPE(5);
+  pdl_enter();
   extern __shared__ int32_t smem[];
+  if (root_tail && blockIdx.x == 0 && threadIdx.x == 0) { root_tail[0] = root_tot[0]; root_tail[1] = root_tot[1]; }
   const int slot = plan->cta_slot[blockIdx.x];
   if (slot < 0) return;
   const int RW = lay->R * 32;                 // used words per array
@@ -177,8 +260,12 @@ hist_accum_cf_kernel(const uint8_t* __restrict__ bins, int64_t n_rows, int last_
   __syncthreads();
   const int pos0 = plan->cta_begin[blockIdx.x];
   const int rows = plan->cta_rows[blockIdx.x];
+  const int nct = plan->b_ncta[slot];
+  const int p0 = plan->b_pbeg[slot], p1 = plan->b_pbeg[slot + 1];
+  const bool direct = nct == 1 && p1 - p0 <= 1;            // this CTA alone holds the node's whole histogram
+  longlong2* out = reinterpret_cast<longlong2*>(level_buf) + (size_t)slot * S;
   int pid = plan->cta_pbase[blockIdx.x];
-  for (int c0 = 0; c0 < rows; c0 += kChunkRows, ++pid) {
+  for (int c0 = 0; c0 < rows || (direct && c0 == 0); c0 += kChunkRows, ++pid) {
     const int crow = min(kChunkRows, rows - c0);
     for (int k = 0; k < nblk; ++k) {
       const int wk = lay->wk[k], ck = lay->ck[k];
@@ -223,6 +310,13 @@ hist_accum_cf_kernel(const uint8_t* __restrict__ bins, int64_t n_rows, int last_
       if (h) atomicAdd(sH + d, h);
     }
     __syncthreads();
+    if (direct) {
+      for (int s = threadIdx.x; s < RW; s += blockDim.x) {
+        const int sl = __ldg(slot_of + s);
+        if (sl >= 0) out[sl] = make_longlong2((long long)sG[s], (long long)sH[s]);
+      }
+      return;
+    }
     int32_t* pp = partials + (size_t)pid * 2 * RW;
     for (int s = threadIdx.x; s < RW; s += blockDim.x) {
       pp[s] = sG[s]; pp[RW + s] = sH[s];
@@ -230,66 +324,58 @@ hist_accum_cf_kernel(const uint8_t* __restrict__ bins, int64_t n_rows, int last_
     }
     __syncthreads();
   }
-}
-
-// level buffer [slot][S][2] int64 (+)= sum over a z-slice of the node's int32 partials, un-permuted
-// through slot_of.  Each thread owns 4 consecutive shared-memory-order words of G and of H (16-byte
-// loads, 4 partials in flight).  With gridDim.z > 1 the z-slices add atomically into a zeroed buffer;
-// with gridDim.z == 1 the result is stored directly.
-__global__ void __launch_bounds__(256) hist_reduce_cf_kernel(const int32_t* __restrict__ partials,
-                                                             const HistPlan* __restrict__ plan, int R, int S,
-                                                             const int32_t* __restrict__ slot_of,
-                                                             int64_t* __restrict__ level_buf) {
-  CB_LEVEL_TRACE_SCOPE(4);
-  const int j = blockIdx.y;
-  if (j >= plan->n_build) return;
-  const int RW = R * 32;
-  const int v = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  if (v >= RW) return;
-  const int p0 = plan->b_pbeg[j], p1 = plan->b_pbeg[j + 1];
-  const int np = p1 - p0, nz = gridDim.z;
-  const int per = (np + nz - 1) / nz;
-  const int pa = p0 + blockIdx.z * per, pb = min(p1, pa + per);
-  long long g[4] = {0, 0, 0, 0}, h[4] = {0, 0, 0, 0};
-  const int32_t* pp = partials + (size_t)pa * 2 * RW + v;
-  int p = pa;
-  for (; p + 4 <= pb; p += 4, pp += (size_t)8 * RW) {
-    int4 a[4], c[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      a[u] = __ldg(reinterpret_cast<const int4*>(pp + (size_t)u * 2 * RW));
-      c[u] = __ldg(reinterpret_cast<const int4*>(pp + (size_t)u * 2 * RW + RW));
-    }
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      g[0] += a[u].x; g[1] += a[u].y; g[2] += a[u].z; g[3] += a[u].w;
-      h[0] += c[u].x; h[1] += c[u].y; h[2] += c[u].z; h[3] += c[u].w;
+  // ---- the node's CTAs meet, then each reduces its slice of the words over all of the node's partials
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    atomicAdd(done + slot, 1u);
+    unsigned spins = 0;
+    while (ld_acquire_u32(done + slot) < (unsigned)nct) {
+      if (++spins > (1u << 22)) { *wait_timeout = 2u; break; }   // cannot happen while the grid is co-resident
+      __nanosleep(32);
     }
   }
-  for (; p < pb; ++p, pp += (size_t)2 * RW) {
-    const int4 a = __ldg(reinterpret_cast<const int4*>(pp));
-    const int4 c = __ldg(reinterpret_cast<const int4*>(pp + RW));
-    g[0] += a.x; g[1] += a.y; g[2] += a.z; g[3] += a.w;
-    h[0] += c.x; h[1] += c.y; h[2] += c.z; h[3] += c.w;
-  }
-  const int4 so = __ldg(reinterpret_cast<const int4*>(slot_of + v));
-  const int sl[4] = {so.x, so.y, so.z, so.w};
-  long long* out = reinterpret_cast<long long*>(level_buf) + (size_t)j * 2 * S;
+  __syncthreads();
+  const int k = (int)blockIdx.x - plan->b_cta0[slot];
+  const int nq = RW >> 2, np = p1 - p0;
+  const int q0 = (int)((long long)nq * k / nct), q1 = (int)((long long)nq * (k + 1) / nct);
+  const int32_t* pbase = partials + (size_t)p0 * 2 * RW;
+  if (np >= 8) {                              // a warp per quad of words, its lanes over the partials
+    for (int q = q0 + warp; q < q1; q += 32) {
+      long long g[4] = {0, 0, 0, 0}, h[4] = {0, 0, 0, 0};
+      for (int p = lane; p < np; p += 32) {
+        const int32_t* pq = pbase + (size_t)p * 2 * RW + 4 * q;
+        const int4 a = __ldcg(reinterpret_cast<const int4*>(pq));
+        const int4 c = __ldcg(reinterpret_cast<const int4*>(pq + RW));
+        g[0] += a.x; g[1] += a.y; g[2] += a.z; g[3] += a.w;
+        h[0] += c.x; h[1] += c.y; h[2] += c.z; h[3] += c.w;
+      }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    if (sl[i] < 0) continue;
-    if (nz == 1) {
-      reinterpret_cast<longlong2*>(out)[sl[i]] = make_longlong2(g[i], h[i]);
-    } else {
-      if (g[i]) atomicAdd(reinterpret_cast<unsigned long long*>(out) + 2 * (size_t)sl[i], (unsigned long long)g[i]);
-      if (h[i]) atomicAdd(reinterpret_cast<unsigned long long*>(out) + 2 * (size_t)sl[i] + 1, (unsigned long long)h[i]);
+      for (int i = 0; i < 4; ++i) { g[i] = warp_sum_i64(g[i]); h[i] = warp_sum_i64(h[i]); }
+      if (lane < 4) {
+        const int sl = __ldg(slot_of + 4 * q + lane);
+        const long long gg = lane == 0 ? g[0] : lane == 1 ? g[1] : lane == 2 ? g[2] : g[3];
+        const long long hh = lane == 0 ? h[0] : lane == 1 ? h[1] : lane == 2 ? h[2] : h[3];
+        if (sl >= 0) out[sl] = make_longlong2(gg, hh);
+      }
+    }
+  } else {                                    // few partials: a thread per quad
+    for (int q = q0 + (int)threadIdx.x; q < q1; q += blockDim.x) {
+      long long g[4] = {0, 0, 0, 0}, h[4] = {0, 0, 0, 0};
+      for (int p = 0; p < np; ++p) {
+        const int32_t* pq = pbase + (size_t)p * 2 * RW + 4 * q;
+        const int4 a = __ldcg(reinterpret_cast<const int4*>(pq));
+        const int4 c = __ldcg(reinterpret_cast<const int4*>(pq + RW));
+        g[0] += a.x; g[1] += a.y; g[2] += a.z; g[3] += a.w;
+        h[0] += c.x; h[1] += c.y; h[2] += c.z; h[3] += c.w;
+      }
+      const int4 so = __ldg(reinterpret_cast<const int4*>(slot_of + 4 * q));
+      if (so.x >= 0) out[so.x] = make_longlong2(g[0], h[0]);
+      if (so.y >= 0) out[so.y] = make_longlong2(g[1], h[1]);
+      if (so.z >= 0) out[so.z] = make_longlong2(g[2], h[2]);
+      if (so.w >= 0) out[so.w] = make_longlong2(g[3], h[3]);
     }
   }
-}
-
-__global__ void zero_i64_kernel(int64_t* p, int64_t n) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) p[i] = 0;
 }
 
 }  // namespace cb

@@ -41,10 +41,14 @@ __device__ __forceinline__ size_t byte_index(const BinsView& v, int64_t row, int
   return (size_t)v.n_rows * 128 * k + (size_t)row * w + (p & 127);
 }
 
+// pos_feature[p]: >= 0 plain feature, -1 padding (code 255), <= -2 group -2 - value of mutually exclusive 2-bin
+// features packed as one code: 0 = no member in bin 1, m + 1 = member m in bin 1 (hist_cf.cuh "storage columns")
 __global__ void __launch_bounds__(256) bin_pack_kernel(const float* __restrict__ X, int64_t n, int f, int64_t ldx,
                                                        const float* __restrict__ cuts,
                                                        const int32_t* __restrict__ n_cuts,
                                                        const int32_t* __restrict__ pos_feature,
+                                                       const int32_t* __restrict__ grp_ptr,
+                                                       const int32_t* __restrict__ grp_feat,
                                                        uint8_t* __restrict__ bins, int wpr, BinsView view) {
   int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (item >= n * wpr) return;
@@ -56,10 +60,69 @@ __global__ void __launch_bounds__(256) bin_pack_kernel(const float* __restrict__
   for (int j = 0; j < 4; ++j) {
     int feat = pos_feature ? __ldg(pos_feature + 4 * w + j) : (4 * w + j < f ? 4 * w + j : -1);
     uint32_t code = CB_MISSING_BIN;
-    if (feat >= 0) code = bin_of(__ldg(x + feat), cuts + (size_t)feat * CB_CUT_STRIDE, __ldg(n_cuts + feat));
+    if (feat >= 0) {
+      code = bin_of(__ldg(x + feat), cuts + (size_t)feat * CB_CUT_STRIDE, __ldg(n_cuts + feat));
+    } else if (feat <= -2 && grp_ptr) {
+      const int g = -2 - feat;
+      const int k0 = __ldg(grp_ptr + g), k1 = __ldg(grp_ptr + g + 1);
+      code = 0;
+      for (int k = k0; k < k1; ++k) {                 // bin 1 of a 2-bin feature <=> x >= its first cut (never NaN in a group)
+        const int mf = __ldg(grp_feat + k);
+        if (__ldg(x + mf) >= __ldg(cuts + (size_t)mf * CB_CUT_STRIDE)) code = (uint32_t)(k - k0 + 1);
+      }
+    }
     out |= code << (8 * j);
   }
   *reinterpret_cast<uint32_t*>(bins + byte_index(view, row, 4 * w)) = out;
+}
+
+// One-hot detection (one-off, before the layout is planned): for up to 64 candidate features (2-bin features, chosen by
+// the host) counts over the rows how often two candidates are in bin 1 together (pair[i * nc + j], i < j) and how often
+// a candidate is missing (miss[i]).  Candidates that never co-occur and are never missing can share one code byte.
+__global__ void __launch_bounds__(256) onehot_pair_kernel(const float* __restrict__ X, int64_t n, int64_t ldx,
+                                                          const float* __restrict__ cuts, const int32_t* __restrict__ cand,
+                                                          int nc, unsigned long long* __restrict__ pair,
+                                                          unsigned long long* __restrict__ miss) {
+  __shared__ unsigned int s_pair[64 * 64];
+  __shared__ unsigned int s_miss[64];
+  __shared__ float s_cut[64];
+  __shared__ int s_feat[64];
+  for (int i = threadIdx.x; i < 64 * 64; i += blockDim.x) s_pair[i] = 0;
+  if (threadIdx.x < 64) {
+    s_miss[threadIdx.x] = 0;
+    const int ft = threadIdx.x < nc ? __ldg(cand + threadIdx.x) : 0;
+    s_feat[threadIdx.x] = ft;
+    s_cut[threadIdx.x] = __ldg(cuts + (size_t)ft * CB_CUT_STRIDE);
+  }
+  __syncthreads();
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < n; row += (int64_t)gridDim.x * blockDim.x) {
+    const float* x = X + row * ldx;
+    unsigned long long on = 0ull;
+    for (int i = 0; i < nc; ++i) {
+      const float v = __ldg(x + s_feat[i]);
+      if (v != v) atomicAdd(&s_miss[i], 1u);
+      else if (v >= s_cut[i]) on |= 1ull << i;
+    }
+    if (__popcll(on) > 1) {
+      unsigned long long a = on;
+      while (a) {
+        const int i = __ffsll((long long)a) - 1;
+        a &= a - 1;
+        unsigned long long b = a;
+        while (b) {
+          const int j = __ffsll((long long)b) - 1;
+          b &= b - 1;
+          atomicAdd(&s_pair[i * 64 + j], 1u);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < 64 * 64; e += blockDim.x) {
+    const int i = e >> 6, j = e & 63;
+    if (i < nc && j < nc && s_pair[e]) atomicAdd(pair + (size_t)i * nc + j, (unsigned long long)s_pair[e]);
+  }
+  if (threadIdx.x < nc && s_miss[threadIdx.x]) atomicAdd(miss + threadIdx.x, (unsigned long long)s_miss[threadIdx.x]);
 }
 
 // position-major copy of the binned matrix: out[p][row] = code of column position p (32 x 32 byte tiles)
@@ -90,6 +153,7 @@ __global__ void __launch_bounds__(256) grad_kernel(const float* __restrict__ mar
                                                    uint32_t tree, int64_t row_offset, int2* __restrict__ gpair,
                                                    unsigned long long* __restrict__ totals,
                                                    const int* __restrict__ tree_ptr) {
+  pdl_enter();
   if (tree_ptr) tree = (uint32_t)*tree_ptr;          // trainer: the device-side round counter
   int64_t G = 0, H = 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -150,6 +214,9 @@ struct HistPlan {               // lives in device memory
   int cta_begin[kMaxGrid];      // first position (in row order) of the CTA's slice
   int cta_rows[kMaxGrid];
   int cta_pbase[kMaxGrid];      // first partial written by the CTA
+  int b_cta0[kMaxBuild];        // first CTA of build slot j; its CTAs are consecutive
+  int b_ncta[kMaxBuild];
+  unsigned int done[kMaxBuild]; // CTAs of build slot j whose partials are complete (conflict-free kernel's in-kernel reduce)
 };
 
 // greedy feature tiling on u32-word boundaries; run once per bin layout
@@ -180,6 +247,7 @@ __device__ inline void plan_ctas(HistPlan* plan, int n_build, const int* begins,
     int per = (counts[j] + nj - 1) / nj;
     per = (per + 31) & ~31;
     plan->b_pbeg[j] = p;
+    plan->b_cta0[j] = b; plan->b_ncta[j] = nj; plan->done[j] = 0u;
     for (int k = 0; k < nj; ++k) {
       int s = min(counts[j], k * per), e = min(counts[j], (k + 1) * per);
       plan->cta_slot[b] = j; plan->cta_begin[b] = begins[j] + s; plan->cta_rows[b] = e - s; plan->cta_pbase[b] = p;

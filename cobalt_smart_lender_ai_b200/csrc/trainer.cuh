@@ -80,6 +80,7 @@ __device__ __forceinline__ void peer_wait(const PeerCtx& pc, TreeState* st, int 
 }
 // tell every peer that `phase` of this level is done here (all earlier writes become visible first)
 __global__ void peer_signal_kernel(PeerCtx pc, const TreeState* st, int level, int phase) {
+  pdl_enter();
   __threadfence_system();
   const int r = threadIdx.x;
   if (r < pc.world) {
@@ -101,10 +102,13 @@ __device__ __forceinline__ TreeOut tree_slice(const TreeOut& base, const TreeSta
 }
 
 __global__ void set_tree_index_kernel(TreeState* st, int idx) { st->tree_index = idx; }
-__global__ void init_state_kernel(TreeState* st) { st->tree_index = 0; st->round_seq = 0; st->peer_timeout = 0; }
+__global__ void init_state_kernel(TreeState* st) {
+  st->tree_index = 0; st->round_seq = 0; st->peer_timeout = 0; st->root_tot[0] = 0; st->root_tot[1] = 0;
+}
 
 __global__ void round_init_kernel(TreeState* st, NodeArrays na, TreeOut to_base, int max_nodes, int n_rows,
                                   HistPlan* plan, int grid) {
+  pdl_enter();
   const TreeOut to = tree_slice(to_base, st, max_nodes);
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < max_nodes) {
@@ -146,8 +150,10 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
                                                                const uint8_t* __restrict__ feature_mask,
                                                                FeatBest* __restrict__ feat_best,
                                                                const int64_t* __restrict__ tail, TreeState* stw,
-                                                               int* __restrict__ group_cnt, int n_groups, PeerCtx pc) {
+                                                               int* __restrict__ group_cnt, int n_groups, PeerCtx pc,
+                                                               const int32_t* __restrict__ feat_code) {
   CB_LEVEL_TRACE_SCOPE(0);
+  pdl_enter();
   __shared__ long long sg[4], sh[4];
   __shared__ unsigned long long skf[4], skb[4];
   const int i = blockIdx.y;
@@ -204,6 +210,19 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
       } else {
         v[k] = lb[b];
       }
+    }
+  }
+  // member of a one-hot group column: only "member set" (bin 1) was accumulated; bin 0 = every other row of the
+  // BUILT node = its totals - bin 1, exactly (int64).  Groups never hold missing values.
+  if (feat_code && __ldg(feat_code + feat) != 0 && tid == 0) {
+    long long Gb = Gt, Hb = Ht;              // level 0: the built node is the root
+    if (level > 0) { const int bn = plan->b_node[j]; Gb = na.G[bn]; Hb = na.H[bn]; }
+    v[0].x = Gb - v[1].x; v[0].y = Hb - v[1].y;
+  }
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int b = 2 * tid + k;
+    if (b < nb) {
       if (par) { const longlong2 q = par[b]; v[k].x = q.x - v[k].x; v[k].y = q.y - v[k].y; }
       mine[b] = v[k];
     }
@@ -296,6 +315,7 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
 // to all ranks, then raises flag 1.  One CTA.
 __global__ void __launch_bounds__(256) peer_publish_kernel(PeerCtx pc, const TreeState* st, int level,
                                                            const FeatBest* __restrict__ feat_best, int f) {
+  pdl_enter();
   const int cnt = st->lvl_count[level];
   for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
     PeerBest pb; pb.key = st->best_key[i]; pb.split_bin = 0; pb.dl = 0; pb.GL = 0; pb.HL = 0;
@@ -329,6 +349,7 @@ struct NodeTable {                        // shared memory, one entry per node o
   int begin[kMaxLevelNodes], count[kMaxLevelNodes];
   int meta[kMaxLevelNodes];               // column position | default_left << 16 | kind << 24
   int bin[kMaxLevelNodes];
+  int mcode[kMaxLevelNodes];              // 0: the column's code is the feature's bin; m + 1: bin = (code == m + 1) (group member)
   float leafL[kMaxLevelNodes], leafR[kMaxLevelNodes];
 };
 
@@ -339,6 +360,7 @@ struct LevelCtx {
   cb_tree_params p;
   NodeArrays na;
   const int32_t* feat_pos;
+  const int32_t* feat_code;               // nullptr: no grouped columns
   PeerCtx pc;
 };
 
@@ -389,6 +411,7 @@ __device__ void build_node_table(NodeTable& nt, const LevelCtx& c, bool want_lea
       const int kind = c.level + 1 == c.max_depth ? 2 : 1;
       nt.meta[i] = c.feat_pos[bf] | (dl << 16) | (kind << 24);
       nt.bin[i] = sbin;
+      nt.mcode[i] = c.feat_code ? c.feat_code[bf] : 0;
       nt.leafL[i] = 0.0f; nt.leafR[i] = 0.0f;
       if (kind == 2 && want_leaves) {
         const float bwL = __double2float_rn(calc_weight(__dmul_rn((double)GL, dg), __dmul_rn((double)HL, dh), c.p));
@@ -396,7 +419,7 @@ __device__ void build_node_table(NodeTable& nt, const LevelCtx& c, bool want_lea
         nt.leafL[i] = __fmul_rn(bwL, c.p.eta); nt.leafR[i] = __fmul_rn(bwR, c.p.eta);
       }
     } else {
-      nt.meta[i] = 0; nt.bin[i] = 0;
+      nt.meta[i] = 0; nt.bin[i] = 0; nt.mcode[i] = 0;
       float leaf = 0.0f;
       if (want_leaves) {
         // same value the level above stored as this node's base weight (recomputed: the finish CTA of
@@ -522,6 +545,7 @@ __global__ void __launch_bounds__(256) part_level_flags_kernel(BinsView view, co
                                                                LevelSegs* segs, uint32_t* __restrict__ flag_bits,
                                                                int* __restrict__ tile_cnt, int* __restrict__ group_cnt) {
   CB_LEVEL_TRACE_SCOPE(1);
+  pdl_enter();
   __shared__ NodeTable nt;
   __shared__ int wsum[8];
   if (c.pc.world > 1) {                             // all ranks' candidates of this level must have arrived
@@ -557,7 +581,11 @@ __global__ void __launch_bounds__(256) part_level_flags_kernel(BinsView view, co
 #pragma unroll
   for (int it = 0; it < IT; ++it) {                 // then the gathers
     code[it] = -1;
-    if (seg[it] >= 0 && (nt.meta[seg[it]] >> 24) == 1) code[it] = code_at(view, bins_cm, row[it], nt.meta[seg[it]] & 0xFFFF);
+    if (seg[it] >= 0 && (nt.meta[seg[it]] >> 24) == 1) {
+      code[it] = code_at(view, bins_cm, row[it], nt.meta[seg[it]] & 0xFFFF);
+      const int mc = nt.mcode[seg[it]];
+      if (mc) code[it] = code[it] == mc ? 1 : 0;
+    }
   }
   int cnt = 0;
 #pragma unroll
@@ -673,6 +701,7 @@ __global__ void __launch_bounds__(256) part_level_scatter_kernel(const uint32_t*
                                                                  TreeState* st, int level, int max_depth, NodeArrays na,
                                                                  HistPlan* plan, int grid, int by_hessian) {
   CB_LEVEL_TRACE_SCOPE(2);
+  pdl_enter();
   __shared__ SegCache sc;
   __shared__ int s_Lb[kMaxLevelNodes], s_nl[kMaxLevelNodes];
   __shared__ PlanSmem psm;
@@ -761,6 +790,7 @@ __global__ void __launch_bounds__(256) final_apply_kernel(BinsView view, const u
                                                           const float* __restrict__ min_vals, TreeOut to, LevelSegs* segs,
                                                           float* __restrict__ margin) {
   CB_LEVEL_TRACE_SCOPE(3);
+  pdl_enter();
   __shared__ NodeTable nt;
   if (c.pc.world > 1) {
     if (threadIdx.x == 0) peer_wait(c.pc, stw, 1, peer_epoch(stw, c.level, 1));
@@ -793,7 +823,11 @@ __global__ void __launch_bounds__(256) final_apply_kernel(BinsView view, const u
 #pragma unroll
   for (int it = 0; it < IT; ++it) {
     code[it] = 0;
-    if (seg[it] >= 0 && (nt.meta[seg[it]] >> 24) == 2) code[it] = code_at(view, bins_cm, row[it], nt.meta[seg[it]] & 0xFFFF);
+    if (seg[it] >= 0 && (nt.meta[seg[it]] >> 24) == 2) {
+      code[it] = code_at(view, bins_cm, row[it], nt.meta[seg[it]] & 0xFFFF);
+      const int mc = nt.mcode[seg[it]];
+      if (mc) code[it] = code[it] == mc ? 1 : 0;
+    }
   }
   float mg[IT];
 #pragma unroll
@@ -813,6 +847,8 @@ __global__ void __launch_bounds__(256) final_apply_kernel(BinsView view, const u
 }
 
 __global__ void round_end_kernel(TreeState* st, int32_t* n_nodes_all) {
+  pdl_enter();
+  if (threadIdx.x == 1) { st->root_tot[0] = 0; st->root_tot[1] = 0; }   // the next round's gradient kernel adds into it
   for (int i = threadIdx.x; i < kMaxLevelNodes; i += blockDim.x) st->best_key[i] = 0ull;
   if (threadIdx.x == 0) {
     n_nodes_all[st->tree_index] = st->n_nodes;

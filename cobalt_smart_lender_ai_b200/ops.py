@@ -32,9 +32,16 @@ def _need_cuda(*ts: torch.Tensor) -> None:
             raise _lib.CobaltError("expected CUDA tensors")
 
 
-def padded_ldb(n_features: int) -> int:
-    """Row stride of the u8 bin matrix: multiple of 16 bytes (whole 32-byte sectors when possible)."""
-    return (n_features + 15) // 16 * 16
+def padded_ldb(n_columns: int) -> int:
+    """Row stride of the u8 bin matrix: whole 128-byte column blocks plus a last block padded to a power of two
+    (>= 16 bytes), so that no block's row ever straddles a 128-byte line (row gathers move whole aligned pieces)."""
+    full, rest = divmod(int(n_columns), 128)
+    w = 0
+    if rest:
+        w = 16
+        while w < rest:
+            w *= 2
+    return 128 * full + w
 
 
 def quant_shifts(wmax: float) -> tuple[int, int]:
@@ -84,32 +91,47 @@ def bin_ptr_of(n_cuts: torch.Tensor) -> torch.Tensor:
     return bp
 
 
-def plan_layout(n_cuts, n_features: int, ldb: int | None = None):
-    """Column placement of the binned matrix (host computation inside the library).
-    Returns (pos_feature int32 [ldb] on the host, conflict_free flag)."""
+def group_arrays(groups):
+    """[[feature, ...], ...] -> (grp_ptr int32 [G + 1], grp_feat int32 [members]) host arrays, or (None, None)."""
+    import numpy as np
+    if not groups:
+        return None, None
+    ptr = np.zeros(len(groups) + 1, np.int32)
+    ptr[1:] = np.cumsum([len(g) for g in groups])
+    return ptr, np.asarray([ft for g in groups for ft in g], np.int32)
+
+
+def plan_layout(n_cuts, n_features: int, ldb: int | None = None, groups=None):
+    """Column placement of the binned matrix (host computation inside the library).  groups: one-hot feature groups
+    that share one code byte each (binned.detect_onehot_groups) or None.
+    Returns (pos_feature int32 [ldb] on the host: >= 0 feature, -1 padding, <= -2 group -2 - v; conflict_free flag)."""
     import numpy as np
     nc = np.ascontiguousarray(n_cuts.cpu().numpy() if isinstance(n_cuts, torch.Tensor) else n_cuts, dtype=np.int32)
-    ldb = ldb or padded_ldb(n_features)
+    gp, gf = group_arrays(groups)
+    n_cols = n_features - (0 if gf is None else len(gf)) + (0 if gp is None else len(gp) - 1)
+    ldb = ldb or padded_ldb(n_cols)
     pos = np.empty(ldb, np.int32)
     flag = C.c_int32(0)
-    check(_lib.load().cb_plan_layout(nc.ctypes.data_as(C.c_void_p), n_features, ldb, pos.ctypes.data_as(C.c_void_p),
+    vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    check(_lib.load().cb_plan_layout(vp(nc), n_features, vp(gp), vp(gf), 0 if gp is None else len(gp) - 1, ldb, vp(pos),
                                      C.byref(flag)))
     return pos, bool(flag.value)
 
 
 def bin_pack(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, ldb: int | None = None,
-             pos_feature: torch.Tensor | None = None, blocked: bool = False) -> torch.Tensor:
-    """K2.  Returns n * ldb bytes as a u8 [n, ldb] tensor; byte p of a row holds feature pos_feature[p]
-    (natural order when None).  blocked=True stores column blocks of 128 bytes as separate arrays
-    (see cb_bin_pack_u8) -- the tensor shape then only carries n and ldb."""
-    _need_cuda(X, cuts, n_cuts, pos_feature)
+             pos_feature: torch.Tensor | None = None, blocked: bool = False, grp_ptr: torch.Tensor | None = None,
+             grp_feat: torch.Tensor | None = None) -> torch.Tensor:
+    """K2.  Returns n * ldb bytes as a u8 [n, ldb] tensor; byte p of a row holds column pos_feature[p]
+    (natural order when None; group columns need grp_ptr / grp_feat).  blocked=True stores column blocks of 128 bytes
+    as separate arrays (see cb_bin_pack_u8) -- the tensor shape then only carries n and ldb."""
+    _need_cuda(X, cuts, n_cuts, pos_feature, grp_ptr, grp_feat)
     assert X.dtype == torch.float32 and X.stride(1) == 1
     n, f = X.shape
-    ldb = ldb or padded_ldb(f)
+    ldb = ldb or (padded_ldb(f) if pos_feature is None else int(pos_feature.numel()))
     assert pos_feature is None or (pos_feature.dtype == torch.int32 and pos_feature.numel() == ldb)
     bins = torch.empty((n, ldb), dtype=torch.uint8, device=X.device)
-    check(_lib.load().cb_bin_pack_u8(_ptr(X), n, f, _ld(X), _ptr(cuts), _ptr(n_cuts), _ptr(pos_feature),
-                                     _ptr(bins), ldb, int(bool(blocked)), _stream()))
+    check(_lib.load().cb_bin_pack_u8(_ptr(X), n, f, _ld(X), _ptr(cuts), _ptr(n_cuts), _ptr(pos_feature), _ptr(grp_ptr),
+                                     _ptr(grp_feat), _ptr(bins), ldb, int(bool(blocked)), _stream()))
     return bins
 
 

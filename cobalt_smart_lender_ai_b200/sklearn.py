@@ -20,6 +20,7 @@ import torch
 from sklearn.base import BaseEstimator, ClassifierMixin
 
 from . import _lib, ops
+from .binned import BinnedMatrix
 from .booster import Booster, base_margin_of
 from .trainer import GpuTrainer
 
@@ -183,15 +184,11 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
             base_score = float(self.base_score) if self.base_score is not None else estimate_base_score(pos_w, neg_w)
             sg, sh = ops.quant_shifts(max(1.0, spw) * wmax_s)
             cuts, n_cuts, min_vals = parallel.sketch_cuts_global(Xd, int(self.max_bin))
-            pos_np, _cf = ops.plan_layout(n_cuts, f)
-            pos = torch.from_numpy(pos_np).to(dev)
-            bins = ops.bin_pack(Xd, cuts, n_cuts, pos_feature=pos, blocked=_cf)
+            bm = BinnedMatrix.from_dense(Xd, cuts, n_cuts)
             del Xd
-            bins_cm = ops.bin_transpose(bins, blocked=_cf)
             bin_ptr = ops.bin_ptr_of(n_cuts)
         return {"dev": dev, "names": names, "n": n, "f": f, "spw": spw, "yd": yd, "wd": wd, "base_score": base_score,
-                "sg": sg, "sh": sh, "row_offset": row_offset, "cuts": cuts, "min_vals": min_vals, "pos": pos, "cf": _cf,
-                "bins": bins, "bins_cm": bins_cm, "bin_ptr": bin_ptr}
+                "sg": sg, "sh": sh, "row_offset": row_offset, "cuts": cuts, "min_vals": min_vals, "bm": bm, "bin_ptr": bin_ptr}
 
     def _boost(self, c: dict, allowed: np.ndarray | None = None) -> dict:
         """n_estimators rounds on prepared bins -> forest (host arrays).  allowed: u8 [f], features a split may use
@@ -205,13 +202,12 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
             masks = np.repeat(a, max(T, 1), axis=0) if masks is None else (masks & a)
         with torch.cuda.device(dev):
             masks_d = None if masks is None else torch.from_numpy(np.ascontiguousarray(masks)).to(dev)
-            tr = GpuTrainer(c["bins"], c["yd"], c["wd"], f, c["bin_ptr"], c["cuts"], c["min_vals"], max_depth=int(self.max_depth),
+            tr = GpuTrainer(c["bm"], c["yd"], c["wd"], f, c["bin_ptr"], c["cuts"], c["min_vals"], max_depth=int(self.max_depth),
                             eta=float(self.learning_rate), reg_lambda=float(self.reg_lambda),
                             reg_alpha=float(self.reg_alpha), gamma=float(self.gamma),
                             min_child_weight=float(self.min_child_weight), scale_pos_weight=c["spw"], sg=c["sg"], sh=c["sh"],
                             subsample=float(self.subsample), seed=seed, max_trees=max(T, 1),
-                            base_margin=base_margin_of(c["base_score"]), row_offset=c["row_offset"], pos_feature=c["pos"],
-                            blocked=c["cf"], bins_cm=c["bins_cm"])
+                            base_margin=base_margin_of(c["base_score"]), row_offset=c["row_offset"])
             tr.boost(T, masks_d)
             forest = tr.forest_numpy()
             self._gpu_launches = tr.launch_count()

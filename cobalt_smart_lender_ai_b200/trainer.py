@@ -25,13 +25,19 @@ FOREST_FIELDS = (("left", torch.int32), ("right", torch.int32), ("parent", torch
 
 
 class GpuTrainer:
-    def __init__(self, bins: torch.Tensor, y: torch.Tensor, weight: torch.Tensor | None, n_features: int,
+    def __init__(self, bins, y: torch.Tensor, weight: torch.Tensor | None, n_features: int,
                  bin_ptr: torch.Tensor, cuts: torch.Tensor, min_vals: torch.Tensor, *, max_depth: int = 6,
                  eta: float = 0.3, reg_lambda: float = 1.0, reg_alpha: float = 0.0, gamma: float = 0.0,
                  min_child_weight: float = 1.0, scale_pos_weight: float = 1.0, sg: int, sh: int,
                  subsample: float = 1.0, seed: int = 0, max_trees: int = 100, base_margin: float = 0.0,
                  row_offset: int = 0, group=None, pos_feature: torch.Tensor | None = None, blocked: bool = False,
                  bins_cm: torch.Tensor | None = None):
+        grp_ptr = grp_feat = None
+        n_groups = 0
+        if hasattr(bins, "natural_codes"):               # a binned.BinnedMatrix carries its own placement
+            bm = bins
+            bins, pos_feature, blocked, bins_cm = bm.bins, bm.pos, bm.blocked, bm.bins_cm
+            grp_ptr, grp_feat, n_groups = bm.grp_ptr, bm.grp_feat, bm.n_groups
         if not bins.is_cuda:
             raise _lib.CobaltError("GpuTrainer needs CUDA tensors: this package has no CPU path")
         self.lib = _lib.load()
@@ -49,6 +55,7 @@ class GpuTrainer:
         self.bin_ptr, self.cuts, self.min_vals = bin_ptr, cuts, min_vals
         self.pos_feature = pos_feature
         self.bins_cm = bins_cm
+        self._grp = (grp_ptr, grp_feat)                  # keep the device arrays alive
         self.margin = torch.full((n,), float(base_margin), dtype=torch.float32, device=self.dev)
         self.forest = {k: torch.zeros((max_trees, self.max_nodes), dtype=dt, device=self.dev) for k, dt in FOREST_FIELDS}
         self.n_nodes = torch.zeros(max_trees, dtype=torch.int32, device=self.dev)
@@ -56,7 +63,7 @@ class GpuTrainer:
                         float(min_child_weight), int(max_depth), int(sg), int(sh))
         self.cfg = TrainConfig(n, ldb, int(row_offset), n_features, total_bins, max_trees, self.world, tp,
                                float(scale_pos_weight), ops.keep_threshold(subsample), int(seed) & 0xFFFFFFFF,
-                               int(bool(blocked)))
+                               int(bool(blocked)), int(n_groups))
         need = C.c_size_t()
         check(self.lib.cb_trainer_workspace_bytes(C.byref(self.cfg), C.byref(need)))
         self.ws = ops.workspace(need.value, self.dev)
@@ -65,7 +72,7 @@ class GpuTrainer:
         p = lambda t: None if t is None else t.data_ptr()  # noqa: E731
         self.buffers = TrainBuffers(p(self.bins), p(self.y), p(self.weight), p(self.margin), p(self.bin_ptr),
                                     p(self.cuts), p(self.min_vals), p(self.pos_feature), p(self.bins_cm), *[p(self.forest[k]) for k, _ in FOREST_FIELDS],
-                                    p(self.n_nodes))
+                                    p(self.n_nodes), p(grp_ptr), p(grp_feat))
         h = C.c_void_p()
         check(self.lib.cb_trainer_create(C.byref(self.cfg), C.byref(self.buffers), wp, wb, C.byref(h)))
         self.handle = h
@@ -114,11 +121,12 @@ class GpuTrainer:
         self.peer_mode = True
 
     def check_peers(self) -> None:
-        if self.peer_mode:
-            flag = C.c_int(0)
-            check(self.lib.cb_trainer_peer_status(self.handle, C.byref(flag)))
-            if flag.value:
-                raise _lib.CobaltError("a wait on a peer GPU timed out during training; results are invalid")
+        """Device-side waits are bounded (a peer GPU's flag; the meeting point of a node's histogram CTAs): a wait
+        that gave up leaves a flag behind, and the forest is then not to be trusted."""
+        flag = C.c_int(0)
+        check(self.lib.cb_trainer_peer_status(self.handle, C.byref(flag)))
+        if flag.value:
+            raise _lib.CobaltError("a device-side wait timed out during training (code %d); results are invalid" % flag.value)
 
     def close(self):
         if getattr(self, "handle", None):

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define CB_VERSION 100
+#define CB_VERSION 200
 #define CB_MISSING_BIN 255 /* u8 code of a missing value (R2) */
 #define CB_MAX_BINS 255    /* real bins per feature (R2) */
 #define CB_CUT_STRIDE 256  /* cuts are stored [n_features][256], padded with +inf */
@@ -54,23 +54,39 @@ int cb_sketch_workspace_bytes(int64_t n_rows, int n_features, size_t* bytes);
 int cb_sketch_cuts(const float* X, int64_t n_rows, int n_features, int64_t ldx, int max_bin, float* cuts,
                    int32_t* n_cuts, float* min_vals, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- one-hot detection on the data (one-off, before the placement is planned).
+ * The reference's feature engineering emits one-hot dummies with pd.get_dummies(..., drop_first=True)
+ * (src/data_preprocessing/feature_engineering.py:142-147): 2-bin features of which at most one per categorical is
+ * set.  For up to 64 candidate features cand[i] (2-bin features, chosen by the host) this ADDS to
+ * pair[i * n_cand + j] (i < j) the number of rows where both are in bin 1 and to miss[i] the number of rows where
+ * candidate i is missing (uint64 device arrays, zero them first).  Candidates that never co-occur and are never
+ * missing can be stored as one code byte (a "group").  When rows are sharded the caller sums the counts over ranks. */
+int cb_onehot_pair_counts(const float* X, int64_t n_rows, int n_features, int64_t ldx, const float* cuts,
+                          const int32_t* cand, int n_cand, uint64_t* pair, uint64_t* miss, void* stream);
+
 /* ---- column placement of the binned matrix (HOST arrays, no device work).
- * pos_feature_host[p] = feature stored in byte p of a binned row, -1 = padding.  Features are
- * dealt to u32 words by descending bin count so that the histogram kernel can give every lane
- * its own shared-memory bank; *conflict_free = 0 means the layout did not fit and the natural
- * order (tiled kernel) is returned.  No reference counterpart (layout is internal to xgboost). */
-int cb_plan_layout(const int32_t* n_cuts_host, int n_features, int64_t ldb, int32_t* pos_feature_host,
-                   int32_t* conflict_free);
+ * A binned row holds one byte per COLUMN: a plain feature, or a group of mutually exclusive 2-bin features packed
+ * as one code (0 = no member in bin 1, m + 1 = member m in bin 1).  Groups: grp_ptr_host [n_groups + 1],
+ * grp_feat_host [grp_ptr[n_groups]] (members, group after group); n_groups = 0 and NULLs for none.
+ * pos_feature_host[p] = column stored in byte p of a binned row: >= 0 a plain feature, -1 padding, <= -2 group
+ * -2 - value.  Columns are dealt to u32 words by descending bin count so that the histogram kernel can give every
+ * lane its own shared-memory bank; *conflict_free = 0 means the layout did not fit and the natural order (tiled
+ * kernel) is returned -- with groups that case is refused (CB_ERR_UNSUPPORTED): plan again without them.
+ * ldb: bytes per binned row, a multiple of 4, >= number of columns.
+ * No reference counterpart (layout is internal to xgboost). */
+int cb_plan_layout(const int32_t* n_cuts_host, int n_features, const int32_t* grp_ptr_host, const int32_t* grp_feat_host,
+                   int n_groups, int64_t ldb, int32_t* pos_feature_host, int32_t* conflict_free);
 
 /* ---- K2 bin-index packing (R2): bins u8, n * ldb bytes, ldb % 4 == 0, pad = 255.
- * pos_feature: i32 [ldb] (device) from cb_plan_layout, or NULL for the natural order.
+ * pos_feature: i32 [ldb] (device) from cb_plan_layout, or NULL for the natural order; grp_ptr / grp_feat: the
+ * groups as device arrays (NULL when pos_feature names no group).
  * blocked = 0: row major [n][ldb].  blocked = 1: column-block major -- bytes [128k, 128k+128) of
  * every row form their own [n][width_k] array at byte offset n * 128 * k (width 128, last block
  * ldb - 128k), so each block streams as whole aligned lines (what the conflict-free histogram reads).
  * Replaces xgboost's GHistIndexMatrix build inside fit (same call sites as K1). */
 int cb_bin_pack_u8(const float* X, int64_t n_rows, int n_features, int64_t ldx, const float* cuts,
-                   const int32_t* n_cuts, const int32_t* pos_feature, uint8_t* bins, int64_t ldb, int blocked,
-                   void* stream);
+                   const int32_t* n_cuts, const int32_t* pos_feature, const int32_t* grp_ptr, const int32_t* grp_feat,
+                   uint8_t* bins, int64_t ldb, int blocked, void* stream);
 
 /* position-major copy of a binned matrix: bins_cm[p * n + row] = byte p of `row`.  Optional input of the
  * trainer: the row partition (K6) reads one byte per row of the split feature, and rows of a node are
@@ -218,6 +234,7 @@ typedef struct {
   uint32_t keep_thresh;
   uint32_t seed;
   int32_t blocked;    /* storage of `bins`: 0 row major, 1 column-block major (see cb_bin_pack_u8) */
+  int32_t n_groups;   /* one-hot groups packed as one column each (cb_plan_layout); 0 = none */
 } cb_train_config;
 
 typedef struct {
@@ -234,6 +251,8 @@ typedef struct {
   int32_t* left; int32_t* right; int32_t* parent; int32_t* split_index; int32_t* split_bin;
   float* split_cond; uint8_t* default_left; float* base_weight; float* loss_chg; float* sum_hess;
   int32_t* n_nodes;        /* [max_trees] */
+  const int32_t* grp_ptr;  /* [n_groups + 1] or NULL */
+  const int32_t* grp_feat; /* [grp_ptr[n_groups]] member features, group after group, or NULL */
 } cb_train_buffers;
 
 typedef struct cb_trainer_s cb_trainer;

@@ -8,6 +8,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from cobalt_smart_lender_ai_b200 import ops, parallel  # noqa: E402
+from cobalt_smart_lender_ai_b200.binned import BinnedMatrix  # noqa: E402
 from cobalt_smart_lender_ai_b200.synth import make_lending  # noqa: E402
 from cobalt_smart_lender_ai_b200.trainer import GpuTrainer  # noqa: E402
 from oracle import oracle as O  # noqa: E402
@@ -28,13 +29,10 @@ def main():
         for mode in ("peer", "nccl"):
             os.environ["COBALT_MULTIGPU"] = mode
             cuts, n_cuts, min_vals = parallel.sketch_cuts_global(X, 256)
-            pos_np, cf = ops.plan_layout(n_cuts, f)
-            pos = torch.from_numpy(pos_np).cuda()
-            bins = ops.bin_pack(X, cuts, n_cuts, pos_feature=pos, blocked=cf)
+            bm = BinnedMatrix.from_dense(X, cuts, n_cuts)        # one-hot groups are agreed on over all ranks
             sg, sh = ops.quant_shifts(max(1.0, spw))
-            tr = GpuTrainer(bins, y, None, f, ops.bin_ptr_of(n_cuts), cuts, min_vals, max_depth=depth, eta=0.3,
-                            scale_pos_weight=spw, sg=sg, sh=sh, max_trees=trees, row_offset=b, pos_feature=pos,
-                            blocked=cf, bins_cm=ops.bin_transpose(bins, blocked=cf))
+            tr = GpuTrainer(bm, y, None, f, ops.bin_ptr_of(n_cuts), cuts, min_vals, max_depth=depth, eta=0.3,
+                            scale_pos_weight=spw, sg=sg, sh=sh, max_trees=trees, row_offset=b)
             assert tr.peer_mode == (mode == "peer")
             print(f"[mgpu] rank {rank} trainer ready mode={mode}", flush=True)
             tr.boost(trees, use_graph=os.environ.get("MGPU_GRAPH", "1") == "1")

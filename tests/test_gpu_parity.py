@@ -571,6 +571,78 @@ def test_estimator_end_to_end(ops, data):
         clf.predict_proba(pd.DataFrame(Xt[:5], columns=names[::-1]))
 
 
+def _train_grouped(ref, X, y, n_trees, spw, masks=None, **kw):
+    """The product's own preparation: K2 on the GPU with one-hot groups packed as one code byte each."""
+    from cobalt_smart_lender_ai_b200.binned import BinnedMatrix
+    from cobalt_smart_lender_ai_b200.trainer import GpuTrainer
+    tp = ref["tp"]
+    bm = BinnedMatrix.from_dense(_dev(X), _dev(ref["cuts"]), _dev(ref["n_cuts"]), **kw)
+    tr = GpuTrainer(bm, _dev(y), None, X.shape[1], _dev(ref["bin_ptr"]), _dev(ref["cuts"]), _dev(ref["min_vals"]),
+                    max_depth=tp.max_depth, eta=tp.eta, gamma=tp.gamma, scale_pos_weight=spw, sg=tp.sg, sh=tp.sh,
+                    max_trees=n_trees, base_margin=O.base_margin_of(ref["base_score"]), group=False)
+    tr.boost(n_trees, None if masks is None else _dev(masks))
+    return tr, bm
+
+
+def test_onehot_groups_one_code_byte_bit_exact(ops):
+    """SURVEY 8f-2 (the part on the hot path): the engineered schema's one-hot dummies are found on the data, a group
+    shares one code byte, 150 columns fit one 128-byte line -- and codes, root histogram, every split, the row order
+    and the margins still equal the oracle's, which reads one byte per feature."""
+    from cobalt_smart_lender_ai_b200.synth import make_lending
+    X, y, names = make_lending(30000, 150, seed=5)
+    X, y = X.numpy(), y.numpy()
+    spw = float((y == 0).sum() / (y == 1).sum())
+    ref = O.fit_reference(X, y, n_estimators=4, max_depth=6, scale_pos_weight=spw, want_rows=True, want_hist=True)
+    tr, bm = _train_grouped(ref, X, y, 4, spw)
+    assert bm.n_groups >= 6 and bm.ldb == 128 and not bm.blocked and bm.cf
+    grouped = {ft for g in bm.groups for ft in g}
+    assert all(ref["n_cuts"][ft] == 2 for ft in grouped) and len(grouped) >= 30
+    assert np.array_equal(bm.natural_codes(), ref["bins"][:, :150])
+    _assert_forest_equal(tr.forest_numpy(), ref["flat"])
+    assert np.array_equal(tr.margin.cpu().numpy().view(np.uint32), ref["margin"].view(np.uint32))
+    assert np.array_equal(tr.node_hist(0).cpu().numpy(), ref["forest"]["root_hist"])
+    assert np.array_equal(_final_rows(ref, tr, ref["bins"]), ref["forest"]["row_order"])
+    # the same fit with the groups switched off gives the same forest (and uses two column blocks)
+    tr2, bm2 = _train_grouped(ref, X, y, 4, spw, group_onehot=False)
+    assert bm2.n_groups == 0 and bm2.ldb == 160
+    _assert_forest_equal(tr2.forest_numpy(), ref["flat"])
+    # per-tree column masks (colsample_bytree / RFE) address member features one by one
+    masks = (np.random.default_rng(3).random((3, 150)) < 0.6).astype(np.uint8)
+    ref3 = O.fit_reference(X, y, n_estimators=3, max_depth=5, scale_pos_weight=spw, feature_masks=masks)
+    tr3, _ = _train_grouped(ref3, X, y, 3, spw, masks=masks)
+    _assert_forest_equal(tr3.forest_numpy(), ref3["flat"])
+
+
+def test_onehot_detection_is_exact():
+    """Grouping is decided on the data: one row where two indicators are both set, or one missing value, keeps a
+    column out of every group; splits on grouped members (forced by the data) send exactly the member's rows right."""
+    from cobalt_smart_lender_ai_b200 import ops as _ops
+    from cobalt_smart_lender_ai_b200.binned import BinnedMatrix, detect_onehot_groups
+    rng = np.random.default_rng(11)
+    n = 20000
+    cat = rng.integers(0, 5, n)                                   # 5 levels -> 4 dummies (drop_first)
+    cat[11] = 1
+    X = np.zeros((n, 9), np.float32)
+    for m in range(4):
+        X[:, m] = cat == m + 1
+    X[:, 4] = rng.random(n) < 0.3                                 # independent indicator: co-occurs with the dummies
+    X[:, 5] = (cat == 0) & (rng.random(n) < 0.5)                  # exclusive with the dummies by construction
+    X[:, 6] = X[:, 5]; X[7, 6] = np.nan                           # ... but has ONE missing value
+    X[:, 7] = X[:, 5]; X[11, 7] = 1.0                             # ... but is set together with dummy 0 ONCE (row 11)
+    X[:, 8] = rng.normal(size=n)
+    y = ((cat == 2) | (X[:, 8] > 1.0)).astype(np.uint8)
+    cuts, nc, mv = O.compute_cuts(X, 256)
+    groups = detect_onehot_groups(_dev(X), _dev(cuts), _dev(nc))
+    assert groups == [[0, 1, 2, 3, 5]], groups
+    ref = O.fit_reference(X, y, n_estimators=3, max_depth=4, scale_pos_weight=1.0, want_rows=True)
+    tr, bm = _train_grouped(ref, X, y, 3, 1.0)
+    assert bm.groups == groups and np.array_equal(bm.natural_codes(), ref["bins"][:, :9])
+    assert 1 in ref["flat"]["split_index"][ref["flat"]["left"] >= 0]          # a member of the group is split on
+    _assert_forest_equal(tr.forest_numpy(), ref["flat"])
+    assert np.array_equal(tr.margin.cpu().numpy().view(np.uint32), ref["margin"].view(np.uint32))
+    assert np.array_equal(_final_rows(ref, tr, ref["bins"]), ref["forest"]["row_order"])
+
+
 def test_full_size_properties(ops):
     """BASELINE size (2.2M x 150): properties that need no oracle run -- histogram additivity
     (parent = left + right, exact), node totals, margin replay through the scoring kernel."""
@@ -579,16 +651,15 @@ def test_full_size_properties(ops):
     from cobalt_smart_lender_ai_b200.trainer import GpuTrainer
     n, f = 2_200_000, 150
     X, y, _ = make_lending(n, f, device="cuda")
+    from cobalt_smart_lender_ai_b200.binned import BinnedMatrix
     cuts, n_cuts, min_vals = ops.sketch_cuts(X, 256)
-    pos_np, cf = ops.plan_layout(n_cuts, f)
-    assert cf
-    pos = torch.from_numpy(pos_np).cuda()
-    bins = ops.bin_pack(X, cuts, n_cuts, pos_feature=pos, blocked=True)
+    bm = BinnedMatrix.from_dense(X, cuts, n_cuts)
+    assert bm.cf and bm.n_groups > 0 and bm.ldb == 128
     bp = ops.bin_ptr_of(n_cuts)
     spw = float(((y == 0).sum() / (y == 1).sum()).item())
     sg, sh = ops.quant_shifts(spw)
-    tr = GpuTrainer(bins, y, None, f, bp, cuts, min_vals, max_depth=6, eta=0.3, scale_pos_weight=spw, sg=sg, sh=sh,
-                    max_trees=3, group=False, pos_feature=pos, blocked=True)
+    tr = GpuTrainer(bm, y, None, f, bp, cuts, min_vals, max_depth=6, eta=0.3, scale_pos_weight=spw, sg=sg, sh=sh,
+                    max_trees=3, group=False)
     tr.boost(3)
     fo = tr.forest_numpy()
     a = int(fo["tree_offsets"][2])

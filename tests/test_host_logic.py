@@ -14,7 +14,7 @@ def test_library_loads_and_exports_every_declared_symbol():
     """The C-ABI library builds/loads without a GPU and exports everything include/*.h declares."""
     from cobalt_smart_lender_ai_b200 import _lib
     lib = _lib.load()
-    assert lib.cb_version() == 100
+    assert lib.cb_version() == 200
     hdr = open(os.path.join(ROOT, "include", "cobalt_gbdt.h")).read()
     declared = set(re.findall(r"^(?:int|void|int64_t|const char\*)\s+(cb_[a-z0-9_]+)\s*\(", hdr, flags=re.M))
     assert declared, "no declarations found"

@@ -91,6 +91,46 @@ def test_hessian_additivity_and_validity(fixture_forest):
     assert min(H[l].min(), H[r].min()) >= float(ff["min_child_weight"])
 
 
+def test_gain_formula_every_node_within_input_rounding(fixture_forest):
+    """R6 on ALL 29 458 internal nodes, no quantile: the stored loss_chg is reproduced from the stored (f32) weights and
+    hessians to within the rounding noise of those inputs, 3.5e-7 of the three gain terms' magnitude.  A factor 1/2, a
+    lambda left out of a denominator or gamma subtracted from the gain would be off by O(1) of that scale."""
+    ff = fixture_forest
+    G, H = _unscaled_G(ff)
+    lam = float(ff["reg_lambda"])
+    internal = np.nonzero(ff["left"] != -1)[0]
+    base = ff["tree_offsets"][np.searchsorted(ff["tree_offsets"], internal, side="right") - 1]
+    l, r = base + ff["left"][internal], base + ff["right"][internal]
+    gain = lambda g, h: g * g / (h + lam)  # noqa: E731
+    gl, gr, gp = gain(G[l], H[l]), gain(G[r], H[r]), gain(G[internal], H[internal])
+    err = np.abs(gl + gr - gp - ff["loss_chg"][internal].astype(np.float64))
+    assert len(err) == 29458 and np.max(err / (gl + gr + gp)) < 3.5e-7
+    for wrong in (0.5 * (gl + gr - gp), gain(G[l], H[l] - lam) + gr - gp):
+        assert np.median(np.abs(wrong - ff["loss_chg"][internal]) / (gl + gr + gp)) > 1e-4
+
+
+def test_validity_boundaries_are_inclusive(fixture_forest):
+    """R7 strictness as far as the shipped model shows it: a child whose hessian sum EQUALS min_child_weight (1.0) was
+    accepted, and every accepted loss_chg is >= gamma = 5 (smallest stored: 5.0035); the oracle's scan accepts
+    H == min_child_weight and rejects anything below."""
+    ff = fixture_forest
+    internal = np.nonzero(ff["left"] != -1)[0]
+    base = ff["tree_offsets"][np.searchsorted(ff["tree_offsets"], internal, side="right") - 1]
+    kids = np.concatenate([base + ff["left"][internal], base + ff["right"][internal]])
+    assert ff["sum_hess"][kids].min() == np.float32(1.0) == np.float32(ff["min_child_weight"])
+    assert ff["loss_chg"][internal].min() >= float(ff["gamma"]) > 0
+    bp = np.array([0, 2], np.int32)
+    cuts = np.full((1, 256), np.inf, np.float32)
+    cuts[0, :2] = [1, 2]
+    mv = np.array([-1], np.float32)
+    tp = O.TreeParams(eta=1.0, reg_lambda=1.0, min_child_weight=1.0, max_depth=3, sg=4, sh=4)
+    h = np.array([[-64, 16], [640, 1600]], np.int64)             # left child: H = 16 * 2^-4 = 1.0 exactly
+    s = O.scan(h, bp, cuts, mv, 576, 1616, tp)
+    assert s["feature"] == 0 and s["split_bin"] == 0 and s["HL"] == 16
+    h[0, 1] = 15                                                   # H = 0.9375 < min_child_weight: no valid split
+    assert O.scan(h, bp, cuts, mv, 576, 1615, tp)["feature"] == -1
+
+
 def test_bfs_numbering(fixture_forest):
     """R9: children are allocated consecutively (right = left + 1) in node-id order."""
     ff = fixture_forest

@@ -27,18 +27,16 @@ import numpy as np  # noqa: E402
 import torch  # noqa: E402
 from cobalt_smart_lender_ai_b200 import ops  # noqa: E402
 from cobalt_smart_lender_ai_b200.synth import make_lending  # noqa: E402
+from cobalt_smart_lender_ai_b200.binned import BinnedMatrix
 from cobalt_smart_lender_ai_b200.trainer import GpuTrainer  # noqa: E402
 
 n, f, depth = int(os.environ.get("ROWS", 2_200_000)), 150, 6
 X, y, _ = make_lending(n, f, device="cuda")
 cuts, n_cuts, min_vals = ops.sketch_cuts(X, 256)
-pos_np, cf = ops.plan_layout(n_cuts, f)
-pos = torch.from_numpy(pos_np).cuda()
-bins = ops.bin_pack(X, cuts, n_cuts, pos_feature=pos, blocked=cf)
-cm = ops.bin_transpose(bins, blocked=cf)
+bm = BinnedMatrix.from_dense(X, cuts, n_cuts)
 sg, sh = ops.quant_shifts(6.75)
-tr = GpuTrainer(bins, y, None, f, ops.bin_ptr_of(n_cuts), cuts, min_vals, max_depth=depth, eta=0.3, scale_pos_weight=6.75,
-                sg=sg, sh=sh, max_trees=16, group=False, pos_feature=pos, blocked=cf, bins_cm=cm)
+tr = GpuTrainer(bm, y, None, f, ops.bin_ptr_of(n_cuts), cuts, min_vals, max_depth=depth, eta=0.3, scale_pos_weight=6.75,
+                sg=sg, sh=sh, max_trees=16, group=False)
 lib = _lib.load()
 lib.cb_debug_level_trace.restype = C.c_int
 lib.cb_debug_level_trace.argtypes = [C.c_void_p, C.c_int]

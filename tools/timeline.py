@@ -9,6 +9,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from cobalt_smart_lender_ai_b200 import ops  # noqa: E402
 from cobalt_smart_lender_ai_b200.synth import make_lending  # noqa: E402
+from cobalt_smart_lender_ai_b200.binned import BinnedMatrix
 from cobalt_smart_lender_ai_b200.trainer import GpuTrainer  # noqa: E402
 
 from cobalt_smart_lender_ai_b200 import parallel  # noqa: E402
@@ -23,14 +24,11 @@ if world > 1:
 r0, r1 = parallel.shard_rows(n, rank, world)
 X, y, _ = make_lending(r1 - r0, f, row_offset=r0, device="cuda")
 cuts, n_cuts, min_vals = parallel.sketch_cuts_global(X, 256)
-pos_np, cf = ops.plan_layout(n_cuts, f)
-pos = torch.from_numpy(pos_np).cuda()
-bins = ops.bin_pack(X, cuts, n_cuts, pos_feature=pos, blocked=cf)
-cm = ops.bin_transpose(bins, blocked=cf)
+bm = BinnedMatrix.from_dense(X, cuts, n_cuts)
 spw = 6.75
 sg, sh = ops.quant_shifts(spw)
-tr = GpuTrainer(bins, y, None, f, ops.bin_ptr_of(n_cuts), cuts, min_vals, max_depth=6, eta=0.3, scale_pos_weight=spw,
-                sg=sg, sh=sh, max_trees=40, group=None if world > 1 else False, pos_feature=pos, blocked=cf, bins_cm=cm,
+tr = GpuTrainer(bm, y, None, f, ops.bin_ptr_of(n_cuts), cuts, min_vals, max_depth=6, eta=0.3, scale_pos_weight=spw,
+                sg=sg, sh=sh, max_trees=40, group=None if world > 1 else False,
                 row_offset=r0)
 tr.boost(10, use_graph=False)
 agg = collections.OrderedDict()
