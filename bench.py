@@ -390,8 +390,9 @@ def run_ours(args):
     y_cpu = y.cpu().numpy()
     peer_mode = bool(tr.peer_mode)
     fo_gpu = tr.forest_numpy() if bins_cpu is not None else None
+    hist_info = tr.layout_info()
     tr.close()
-    layout = {"bytes_per_row": bm.ldb, "onehot_groups": [len(g) for g in bm.groups], "conflict_free": bool(bm.cf)}
+    layout = {"bytes_per_row": bm.ldb, "onehot_groups": [len(g) for g in bm.groups], "conflict_free": bool(bm.cf), "histogram_kernel": hist_info}
     del tr, bm
 
     # ---- e2e: the public API with HOST buffers (H2D of X, sketch, binning, ROUNDS_CFG rounds, D2H of the forest)

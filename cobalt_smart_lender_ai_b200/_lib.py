@@ -128,6 +128,7 @@ _SIGS = {
     "cb_trainer_workspace_bytes": (C.c_int, [C.POINTER(TrainConfig), C.POINTER(_SZ)]),
     "cb_trainer_create": (C.c_int, [C.POINTER(TrainConfig), C.POINTER(TrainBuffers), _VP, _SZ, C.POINTER(_VP)]),
     "cb_trainer_destroy": (None, [_VP]),
+    "cb_trainer_layout_info": (C.c_int, [_VP, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "cb_trainer_boost_round": (C.c_int, [_VP, _I, _VP, _VP]),
     "cb_trainer_round_begin": (C.c_int, [_VP, _I, _VP, _VP]),
     "cb_trainer_level_hist": (C.c_int, [_VP, _I, _VP]),

@@ -88,6 +88,17 @@ inline bool plan_positions(const int32_t* n_cuts, int f, const GroupTable& gt, i
   for (int64_t p = 0; p < ldb; ++p) pos_feature[p] = -1;
   const int W = (nc + 3) / 4;
   if ((int64_t)W * 4 > ldb) return false;
+  if (ldb <= 128) {
+    // one column block: use every word of the row (fewer columns per lane = fewer shared-memory rows) and deal the
+    // sorted columns in serpentine order, which evens out the lanes' bin totals (the tallest lane sets the row count R)
+    const int Wa = (int)(ldb / 4);
+    for (int r = 0; r < nc; ++r) {
+      const int j = r / Wa, q = r % Wa;
+      const int word = (j & 1) ? Wa - 1 - q : q;
+      pos_feature[word * 4 + j] = order[idx[r]];
+    }
+    return true;
+  }
   int next = 0;
   for (int k = 0; k * 32 < W; ++k) {
     const int wk = std::min(32, W - 32 * k);
@@ -193,15 +204,18 @@ inline bool build_cf_tables(const int32_t* bin_ptr, const int32_t* pos_feature, 
 constexpr int kCfHOffWords = 28672;            // H array at a fixed +112 KB: an immediate in the ATOMS address
 constexpr int kCfMaxRows = kCfHOffWords / 32;  // 896 rows of 32 banks per array
 constexpr int kCfSmemBytes = 2 * kCfHOffWords * 4;
-
 __device__ __forceinline__ uint32_t ldg_nc_u32(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
   return v;
 }
-
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 // one byte of a bin word: clamp the code to the feature's bin count (255 = missing lands in the
-// row after the last bin, which the reduce kernel ignores) and add (g, h) in the lane's own bank.
+// row after the last bin, which the reduce step ignores) and add (g, h) in the lane's own bank.
 // 5 issue slots per byte: PRMT, VIMNMX, IMAD, 2 x ATOMS; no predicates, no branches.
 template <int POS>
 __device__ __forceinline__ void cf_add_byte_at(uint32_t word, uint32_t nb, uint32_t base, int g, int h) {
@@ -218,15 +232,8 @@ __device__ __forceinline__ void cf_add_byte_at(uint32_t word, uint32_t nb, uint3
       : "r"(word), "n"(POS), "r"(nb), "r"(base), "r"(g), "r"(h)
       : "memory");
 }
-
-__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-
-// 1024 threads = 32 warps; warp w takes row groups w, w + 32, ... of the CTA's slice, one column
-// block after the other (each block is its own contiguous array: block-major storage).
+// 1024 threads = 32 warps; warp w takes row groups w, w + 32, ... of the CTA's slice, one column block after the other
+// (each block is its own contiguous array: block-major storage), UNROLL rows in flight per warp.
 //
 // The reduction to the int64 level buffer happens in the same launch.  The grid never exceeds one CTA per SM, so
 // all of a node's CTAs are resident together and may wait for each other:
@@ -246,7 +253,7 @@ hist_accum_cf_kernel(const uint8_t* __restrict__ bins, int64_t n_rows, int last_
                      const long long* __restrict__ root_tot, int64_t* __restrict__ root_tail) {
   CB_LEVEL_TRACE_SCOPE(5);
   pdl_enter();
-  extern __shared__ int32_t smem[];
+  extern __shared__ __align__(16) int32_t smem[];
   if (root_tail && blockIdx.x == 0 && threadIdx.x == 0) { root_tail[0] = root_tot[0]; root_tail[1] = root_tot[1]; }
   const int slot = plan->cta_slot[blockIdx.x];
   if (slot < 0) return;
@@ -281,6 +288,17 @@ hist_accum_cf_kernel(const uint8_t* __restrict__ bins, int64_t n_rows, int last_
         nbj[j] = (uint32_t)lay->nbj[k][lane][j];
       }
       const int ilast = crow - 1;
+      // gathered rows: the row ids of the NEXT step are fetched while this step's rows are in flight, so a step costs
+      // one memory latency (rows + gradient pairs), not two in a row (ids, then rows)
+      uint32_t rn[UNROLL];
+      auto fetch_ids = [&](int g0) {
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+          const int i = (g0 + 32 * u) * ck + rslot;
+          rn[u] = __ldg(row_idx + pos0 + c0 + max(min(i, ilast), 0));
+        }
+      };
+      if (!IDENTITY && warp * ck < crow) fetch_ids(warp);
       for (int g0 = warp; g0 * ck < crow; g0 += 32 * UNROLL) {
         uint32_t wv[UNROLL];
         int2 gp[UNROLL];
@@ -288,11 +306,12 @@ hist_accum_cf_kernel(const uint8_t* __restrict__ bins, int64_t n_rows, int last_
         for (int u = 0; u < UNROLL; ++u) {
           const int i = (g0 + 32 * u) * ck + rslot;
           const int pos = pos0 + c0 + min(i, ilast);                 // clamped: always a valid row, no branch
-          const uint32_t r = IDENTITY ? (uint32_t)pos : __ldg(row_idx + pos);
+          const uint32_t r = IDENTITY ? (uint32_t)pos : rn[u];
           wv[u] = ldg_nc_u32(reinterpret_cast<const uint32_t*>(bbase + (size_t)r * bw));
           gp[u] = __ldg(gpair + r);
           if (!active || i > ilast) gp[u] = make_int2(0, 0);         // adds zero: harmless
         }
+        if (!IDENTITY && (g0 + 32 * UNROLL) * ck < crow) fetch_ids(g0 + 32 * UNROLL);
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) {
           cf_add_byte_at<0>(wv[u], nbj[0], base[0], gp[u].x, gp[u].y);
@@ -318,16 +337,17 @@ hist_accum_cf_kernel(const uint8_t* __restrict__ bins, int64_t n_rows, int last_
       return;
     }
     int32_t* pp = partials + (size_t)pid * 2 * RW;
+    const bool more = c0 + kChunkRows < rows;
     for (int s = threadIdx.x; s < RW; s += blockDim.x) {
       pp[s] = sG[s]; pp[RW + s] = sH[s];
-      sG[s] = 0; sH[s] = 0;
+      if (more) { sG[s] = 0; sH[s] = 0; }
     }
     __syncthreads();
   }
-  // ---- the node's CTAs meet, then each reduces its slice of the words over all of the node's partials
-  __threadfence();
-  __syncthreads();
+  // ---- the node's CTAs meet (one fence by the signalling thread, after the CTA barrier, publishes all of the CTA's
+  // stores), then each reduces its slice of the words over all of the node's partials
   if (threadIdx.x == 0) {
+    __threadfence();
     atomicAdd(done + slot, 1u);
     unsigned spins = 0;
     while (ld_acquire_u32(done + slot) < (unsigned)nct) {
@@ -336,45 +356,66 @@ hist_accum_cf_kernel(const uint8_t* __restrict__ bins, int64_t n_rows, int last_
     }
   }
   __syncthreads();
+  // Slice of this CTA: quads [q0, q1) of the node's words.  Threads form a (quad, partial group) grid so that both
+  // a node with many partials and few quads per CTA (the root) and one with few partials and many quads keep every
+  // thread busy with independent 16-byte loads; group sums meet in shared memory (free now), one thread per word
+  // adds them and writes the slot.
   const int k = (int)blockIdx.x - plan->b_cta0[slot];
   const int nq = RW >> 2, np = p1 - p0;
   const int q0 = (int)((long long)nq * k / nct), q1 = (int)((long long)nq * (k + 1) / nct);
   const int32_t* pbase = partials + (size_t)p0 * 2 * RW;
-  if (np >= 8) {                              // a warp per quad of words, its lanes over the partials
-    for (int q = q0 + warp; q < q1; q += 32) {
+  long long* sacc = reinterpret_cast<long long*>(smem);          // [G][Q][8], G * Q <= 1024
+  // partial groups: enough that no thread walks more than ~8 partials in a row (two rounds of 4 loads in flight),
+  // and as few as possible otherwise so that one pass covers up to 1024 quads
+  int Gw = (np + 7) >> 3;
+  Gw = Gw < 1 ? 1 : (Gw > 32 ? 32 : Gw);
+  const int QT = (int)blockDim.x / Gw;                           // quads per pass
+  for (int qa = q0; qa < q1; qa += QT) {
+    const int Q = min(QT, q1 - qa);
+    int G = min(np, (int)blockDim.x / Q);
+    G = G < 1 ? 1 : G;
+    const int t = threadIdx.x;
+    const int pg = t / Q, qi = t - pg * Q;
+    if (pg < G) {
       long long g[4] = {0, 0, 0, 0}, h[4] = {0, 0, 0, 0};
-      for (int p = lane; p < np; p += 32) {
-        const int32_t* pq = pbase + (size_t)p * 2 * RW + 4 * q;
-        const int4 a = __ldcg(reinterpret_cast<const int4*>(pq));
-        const int4 c = __ldcg(reinterpret_cast<const int4*>(pq + RW));
-        g[0] += a.x; g[1] += a.y; g[2] += a.z; g[3] += a.w;
-        h[0] += c.x; h[1] += c.y; h[2] += c.z; h[3] += c.w;
-      }
+      const int32_t* pq = pbase + 4 * (size_t)(qa + qi);
+      int p = pg;
+      for (; p + 3 * G < np; p += 4 * G) {                       // 4 partials (8 loads) in flight
+        int4 a[4], c[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { g[i] = warp_sum_i64(g[i]); h[i] = warp_sum_i64(h[i]); }
-      if (lane < 4) {
-        const int sl = __ldg(slot_of + 4 * q + lane);
-        const long long gg = lane == 0 ? g[0] : lane == 1 ? g[1] : lane == 2 ? g[2] : g[3];
-        const long long hh = lane == 0 ? h[0] : lane == 1 ? h[1] : lane == 2 ? h[2] : h[3];
-        if (sl >= 0) out[sl] = make_longlong2(gg, hh);
+        for (int u = 0; u < 4; ++u) {
+          a[u] = __ldcg(reinterpret_cast<const int4*>(pq + (size_t)(p + u * G) * 2 * RW));
+          c[u] = __ldcg(reinterpret_cast<const int4*>(pq + (size_t)(p + u * G) * 2 * RW + RW));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          g[0] += a[u].x; g[1] += a[u].y; g[2] += a[u].z; g[3] += a[u].w;
+          h[0] += c[u].x; h[1] += c[u].y; h[2] += c[u].z; h[3] += c[u].w;
+        }
       }
-    }
-  } else {                                    // few partials: a thread per quad
-    for (int q = q0 + (int)threadIdx.x; q < q1; q += blockDim.x) {
-      long long g[4] = {0, 0, 0, 0}, h[4] = {0, 0, 0, 0};
-      for (int p = 0; p < np; ++p) {
-        const int32_t* pq = pbase + (size_t)p * 2 * RW + 4 * q;
-        const int4 a = __ldcg(reinterpret_cast<const int4*>(pq));
-        const int4 c = __ldcg(reinterpret_cast<const int4*>(pq + RW));
+      for (; p < np; p += G) {
+        const int4 a = __ldcg(reinterpret_cast<const int4*>(pq + (size_t)p * 2 * RW));
+        const int4 c = __ldcg(reinterpret_cast<const int4*>(pq + (size_t)p * 2 * RW + RW));
         g[0] += a.x; g[1] += a.y; g[2] += a.z; g[3] += a.w;
         h[0] += c.x; h[1] += c.y; h[2] += c.z; h[3] += c.w;
       }
-      const int4 so = __ldg(reinterpret_cast<const int4*>(slot_of + 4 * q));
-      if (so.x >= 0) out[so.x] = make_longlong2(g[0], h[0]);
-      if (so.y >= 0) out[so.y] = make_longlong2(g[1], h[1]);
-      if (so.z >= 0) out[so.z] = make_longlong2(g[2], h[2]);
-      if (so.w >= 0) out[so.w] = make_longlong2(g[3], h[3]);
+      long long* d = sacc + ((size_t)pg * Q + qi) * 8;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { d[2 * i] = g[i]; d[2 * i + 1] = h[i]; }
     }
+    __syncthreads();
+    for (int w = threadIdx.x; w < 4 * Q; w += blockDim.x) {      // word w of the pass: add the groups, write the slot
+      const int sl = __ldg(slot_of + 4 * qa + w);
+      if (sl < 0) continue;
+      const int qi2 = w >> 2, i = w & 3;
+      long long gg = 0, hh = 0;
+      for (int e = 0; e < G; ++e) {
+        const long long* d = sacc + ((size_t)e * Q + qi2) * 8 + 2 * i;
+        gg += d[0]; hh += d[1];
+      }
+      out[sl] = make_longlong2(gg, hh);
+    }
+    __syncthreads();
   }
 }
 

@@ -216,6 +216,7 @@ struct HistPlan {               // lives in device memory
   int cta_pbase[kMaxGrid];      // first partial written by the CTA
   int b_cta0[kMaxBuild];        // first CTA of build slot j; its CTAs are consecutive
   int b_ncta[kMaxBuild];
+  int min_rows;                 // rows a CTA should at least get (0: 256); set once at creation
   unsigned int done[kMaxBuild]; // CTAs of build slot j whose partials are complete (conflict-free kernel's in-kernel reduce)
 };
 
@@ -233,7 +234,10 @@ __global__ void plan_tiles_kernel(const int32_t* __restrict__ bin_ptr, int f, in
   if (nt < kMaxTiles) plan->tiles[nt] = TileInfo{w0, words, s0, bin_ptr[f]};
   ++nt;
   plan->n_tiles = min(nt, kMaxTiles);
+  plan->min_rows = 0;
 }
+
+__global__ void plan_set_min_rows_kernel(HistPlan* plan, int min_rows) { plan->min_rows = min_rows; }
 
 // distributes `grid` CTAs over the build nodes proportionally to their row counts
 __device__ inline void plan_ctas(HistPlan* plan, int n_build, const int* begins, const int* counts, int grid) {
@@ -242,7 +246,8 @@ __device__ inline void plan_ctas(HistPlan* plan, int n_build, const int* begins,
   int spare = grid - n_build, b = 0, p = 0;
   for (int j = 0; j < n_build; ++j) {
     int nj = 1 + (total > 0 ? (int)((long long)spare * counts[j] / total) : 0);
-    int need = (counts[j] + 255) / 256;                     // at least 256 rows per CTA (2 warp iterations per column block)
+    const int mr = plan->min_rows > 0 ? plan->min_rows : 256;
+    int need = (counts[j] + mr - 1) / mr;                   // at least `mr` rows per CTA: every CTA pays a fixed zero / flush / reduce
     nj = max(1, min(nj, need));
     int per = (counts[j] + nj - 1) / nj;
     per = (per + 31) & ~31;

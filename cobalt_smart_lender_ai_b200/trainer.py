@@ -238,6 +238,11 @@ class GpuTrainer:
         check(self.lib.cb_trainer_profile_end_sync(self.handle, ms, names, 96, C.byref(n)))
         return [(names[i].decode(), float(ms[i])) for i in range(n.value)]
 
+    def layout_info(self) -> dict:
+        a, b, d = C.c_int(), C.c_int(), C.c_int()
+        check(self.lib.cb_trainer_layout_info(self.handle, C.byref(a), C.byref(b), C.byref(d)))
+        return {"conflict_free": bool(a.value), "smem_rows": b.value, "smem_bytes": d.value}
+
     def launch_count_raw(self) -> int:
         return int(self.lib.cb_trainer_launch_count(self.handle))
 

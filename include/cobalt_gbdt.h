@@ -301,6 +301,9 @@ int cb_trainer_last_hist_timing_sync(cb_trainer* tr, float* ms_accum, float* ms_
  * calls above, then profile_end_sync returns the elapsed ms between consecutive launches and their names */
 int cb_trainer_profile_begin(cb_trainer* tr);
 int cb_trainer_profile_end_sync(cb_trainer* tr, float* ms, const char** names, int capacity, int* n);
+/* which histogram kernel this trainer runs: conflict-free layout or the tiled fallback, shared-memory rows of 32 banks
+ * per array (R), dynamic shared memory per CTA */
+int cb_trainer_layout_info(cb_trainer* tr, int* conflict_free, int* smem_rows, int* smem_bytes);
 /* kernels launched by this trainer so far (bench.py's gpu_launches) */
 int64_t cb_trainer_launch_count(cb_trainer* tr);
 
