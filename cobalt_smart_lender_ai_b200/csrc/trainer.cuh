@@ -201,10 +201,17 @@ __global__ void __launch_bounds__(128) scan_level_fused_kernel(const int64_t* __
     v[k] = make_longlong2(0, 0);
     if (b < nb) {
       if (pc.world > 1) {                    // the fused collective: add this slice of every rank's histogram
+        // all peers' loads are issued before the first add: one NVLink round trip per bin, not one per rank
         long long ag = 0, ah = 0;
-        for (int r = 0; r < pc.world; ++r) {
-          const longlong2 q = __ldcv(reinterpret_cast<const longlong2*>(pc.peer_level_buf[r]) + (size_t)j * S + b0 + b);
-          ag += q.x; ah += q.y;
+        const size_t off = (size_t)j * S + b0 + b;
+        for (int r0 = 0; r0 < pc.world; r0 += 8) {
+          longlong2 q[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            q[u] = (r0 + u < pc.world) ? __ldcv(reinterpret_cast<const longlong2*>(pc.peer_level_buf[r0 + u]) + off)
+                                       : make_longlong2(0, 0);
+#pragma unroll
+          for (int u = 0; u < 8; ++u) { ag += q[u].x; ah += q[u].y; }
         }
         v[k] = make_longlong2(ag, ah);
       } else {
