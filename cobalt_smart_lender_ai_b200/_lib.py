@@ -116,6 +116,7 @@ _SIGS = {
     "cb_split_scan_noalloc": (C.c_int, [_VP, _VP, _I, _VP, _VP, _VP, C.POINTER(TreeParams), _VP, _VP, _VP]),
     "cb_partition_workspace_bytes": (C.c_int, [_I64, C.POINTER(_SZ)]),
     "cb_partition_stable": (C.c_int, [_VP, _I64, _VP, _I64, _I, _I, _I, _VP, _VP, _VP, _SZ, _VP]),
+    "cb_leaf_update": (C.c_int, [_VP, _VP, _I64, _F, _VP]),
     "cb_predict": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _I, _F, _VP, _VP, _VP]),
     "cb_predict_heap_plan": (C.c_int, [_I, _I, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "cb_predict_heap": (C.c_int, [_VP, _I64, _I, _I64, _VP, _VP, _I, _I, _F, _VP, _VP, _VP]),

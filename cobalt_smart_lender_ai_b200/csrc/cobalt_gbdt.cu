@@ -403,6 +403,15 @@ int cb_partition_stable(const uint8_t* bins, int64_t ldb, const uint32_t* seg_in
   return CB_OK;
 }
 
+// ---------------------------------------------------------------------------- K7
+int cb_leaf_update(float* margin, const uint32_t* row_idx, int64_t count, float leaf_value, void* stream) {
+  if (!margin || count < 0) return fail(CB_ERR_INVALID, "cb_leaf_update: bad arguments");
+  if (count == 0) return CB_OK;
+  leaf_update_kernel<<<ceil_div(count, 256), 256, 0, (cudaStream_t)stream>>>(margin, row_idx, count, leaf_value);
+  CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
 // ---------------------------------------------------------------------------- K8
 int cb_predict(const float* X, int64_t n, int f, int64_t ldx, const uint64_t* nodes, const int32_t* tree_off,
                int n_trees, float base_margin, float* out_margin, float* out_proba, void* stream) {
@@ -431,8 +440,8 @@ static int heap_chunk_trees(const DeviceInfo& di, int f, int depth, int* rows_ou
   const int NI = (1 << depth) - 1, NL = 1 << depth;
   const int per_tree = NI * 8 + NL * 4;
   // two CTAs per SM (one stages its row tile while the other walks trees) when 128-row tiles fit
-  const char* env = getenv("COBALT_PRED_ROWS");
-  int rows = env ? atoi(env) : 128;
+  static const int env_rows = [] { const char* e = getenv("COBALT_PRED_ROWS"); return e ? atoi(e) : 128; }();   // read once
+  int rows = env_rows;
   if (rows != 256 && rows != 128 && rows != 64 && rows != 32) rows = 128;
   for (;;) {
     const int64_t tile = (((int64_t)f * rows * 4 + 127) & ~(int64_t)127);
@@ -484,8 +493,8 @@ int cb_predict_heap(const float* X, int64_t n, int f, int64_t ldx, const uint64_
     CB_CUDA(cudaFuncSetAttribute(predict_heap_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, di.smem_optin - 1024));
     attr_dev = di.device;
   }
-  const char* ilp_env = getenv("COBALT_PRED_ILP");
-  if (ilp_env && atoi(ilp_env) == 4)
+  static const int env_ilp = [] { const char* e = getenv("COBALT_PRED_ILP"); return e ? atoi(e) : 8; }();          // read once
+  if (env_ilp == 4)
     predict_heap_kernel<4><<<ceil_div(n, rows), rows, smem, (cudaStream_t)stream>>>(
         X, n, f, ldx, reinterpret_cast<const uint2*>(nodes), leaf, n_trees, depth, chunk, base_margin, out_margin, out_proba);
   else
@@ -521,11 +530,8 @@ static int q8_plane_base(const DeviceInfo& di, uint32_t* base) {
   std::lock_guard<std::mutex> lock(mu);
   const int d = di.device & 63;
   if (!have[d]) {
-    uint32_t* dv = nullptr;
-    CB_CUDA(cudaMalloc(&dv, sizeof(uint32_t)));
-    smem_base_probe_kernel<<<1, 1, 1024>>>(dv);
-    cudaError_t e = cudaMemcpy(&cached[d], dv, sizeof(uint32_t), cudaMemcpyDeviceToHost);
-    cudaFree(dv);
+    smem_base_probe_kernel<<<1, 1, 1024>>>();
+    cudaError_t e = cudaMemcpyFromSymbol(&cached[d], g_smem_base_probe, sizeof(uint32_t));   // synchronises; no allocation
     if (e != cudaSuccess) return fail(CB_ERR_CUDA, "cb_predict_q8_plan: probe failed: %s", cudaGetErrorString(e));
     have[d] = true;
   }
@@ -579,6 +585,11 @@ int cb_predict_q8(const uint8_t* codes, int64_t n, int f, int64_t ldc, const uin
   int smem = 0;
   const int chunk = q8_chunk_trees(di, f, depth, ldc, &smem);
   if (chunk < 8) return fail(CB_ERR_UNSUPPORTED, "cb_predict_q8: %d features at depth %d do not fit shared memory", f, depth);
+  uint32_t want_base = 0;
+  if ((rc = q8_plane_base(di, &want_base))) return rc;
+  if (want_base != plane_base)
+    return fail(CB_ERR_INVALID, "cb_predict_q8: plane_base %u is not this device's (%u): lay the forest out with cb_predict_q8_plan on this device",
+                plane_base, want_base);
   auto launch = [&](auto kernel) -> int {
     CB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, di.smem_optin - 1024));
     kernel<<<ceil_div(n, 128), 128, smem, (cudaStream_t)stream>>>(codes, n, f, ldc, forest, n_trees, chunk, base_margin,

@@ -779,7 +779,8 @@ __global__ void __launch_bounds__(256) bin_rows_q8_kernel(const float* __restric
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int i = threadIdx.x; i < 32 * 256; i += 256) {
     const int cf = i >> 8, k = i & 255;
-    tab[cf * 257 + k] = (c0 + cf < f) ? __ldg(cuts + (size_t)(c0 + cf) * CB_CUT_STRIDE + k) : 0.0f;
+    const bool real = c0 + cf < f && k < __ldg(n_cuts + c0 + cf);        // everything else is +inf whatever the caller padded with
+    tab[cf * 257 + k] = real ? __ldg(cuts + (size_t)(c0 + cf) * CB_CUT_STRIDE + k) : __int_as_float(0x7f800000);
   }
   __syncthreads();
   const int c = c0 + lane;
@@ -790,27 +791,27 @@ __global__ void __launch_bounds__(256) bin_rows_q8_kernel(const float* __restric
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta, r1 = min(n, r0 + rows_per_cta);
   for (int64_t rb = r0 + warp * 4; rb < r1; rb += 32) {       // 8 warps x 4 rows in flight
     float x[4];
-    int lo[4];
+    const float* lo[4];                                       // &table[number of thresholds <= x found so far]
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int64_t r = min(rb + u, r1 - 1);
       x[u] = on ? __ldg(X + r * ldx + c) : 0.0f;
-      lo[u] = 0;
+      lo[u] = my;
     }
+    // branch-free binary search, 3 instructions per probe: the table is padded with +inf up to 256 entries, so a probe
+    // past the feature's last threshold simply fails (it succeeds only for x = +inf, which the final clamp undoes)
 #pragma unroll
     for (int s = 128; s > 0; s >>= 1) {
       if (s > nc_max) continue;                              // warp uniform: a slab of one-hot columns needs one probe
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int probe = lo[u] + s;
-        if (probe <= nc && my[probe - 1] <= x[u]) lo[u] = probe;
-      }
+      for (int u = 0; u < 4; ++u)
+        if (lo[u][s - 1] <= x[u]) lo[u] += s;
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int64_t r = rb + u;
       if (on && r < r1) {
-        uint32_t code = (uint32_t)(lo[u] == nc ? nc - 1 : lo[u]);   // same clamp as K2 (never taken with a +inf sentinel)
+        uint32_t code = (uint32_t)min((int)(lo[u] - my), nc - 1);   // same clamp as K2
         if (x[u] != x[u]) code = CB_MISSING_BIN;
         codes[r * ldc + c] = (uint8_t)code;
       }
@@ -818,10 +819,21 @@ __global__ void __launch_bounds__(256) bin_rows_q8_kernel(const float* __restric
   }
 }
 
-// shared-window address of the dynamic shared memory of a kernel without static shared memory
-__global__ void smem_base_probe_kernel(uint32_t* out) {
+// shared-window address of the dynamic shared memory of a kernel without static shared memory; the answer goes to a
+// word in the module's device image (read back with cudaMemcpyFromSymbol: the probe allocates nothing)
+__device__ uint32_t g_smem_base_probe;
+__global__ void smem_base_probe_kernel() {
   extern __shared__ __align__(128) uint8_t probe_s[];
-  *out = (uint32_t)__cvta_generic_to_shared(probe_s);
+  g_smem_base_probe = (uint32_t)__cvta_generic_to_shared(probe_s);
+}
+
+// K7, standalone form: every row of a leaf's segment takes the leaf value (R10: m_r += leaf[node(r)])
+__global__ void __launch_bounds__(256) leaf_update_kernel(float* __restrict__ margin, const uint32_t* __restrict__ rows,
+                                                          int64_t count, float leaf) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  const int64_t r = rows ? (int64_t)rows[i] : i;
+  margin[r] = __fadd_rn(margin[r], leaf);
 }
 
 constexpr int kQ8Stages = 2;               // tree-chunk buffers: one being walked, one in flight
@@ -847,7 +859,16 @@ __global__ void __launch_bounds__(128, 4) predict_q8_kernel(const uint8_t* __res
   // the planes start at the bottom of the CTA's shared window, whose address (plane_base, cb_predict_q8_plan) is
   // already added to every node's offset field, so "(node & 0xFFFF) | row byte" IS the shared address of the code.
   extern __shared__ __align__(128) uint8_t q8s[];
-  if ((uint32_t)__cvta_generic_to_shared(q8s) != plane_base) __trap();   // forest was laid out for another window
+  if ((uint32_t)__cvta_generic_to_shared(q8s) != plane_base) {
+    // the forest was laid out for another shared window (the host checks plane_base before launching, so this cannot
+    // happen through the C ABI): answer NaN rather than walk wrong addresses or poison the context with a trap
+    const int64_t rr = (int64_t)blockIdx.x * 128 + threadIdx.x;
+    if (rr < n) {
+      if (out_margin) out_margin[rr] = __int_as_float(0x7fc00000);
+      if (out_proba) out_proba[rr] = __int_as_float(0x7fc00000);
+    }
+    return;
+  }
   constexpr int R = 128;
   constexpr int depth = DEPTH;
   constexpr uint32_t TB = 8u << DEPTH;              // bytes per tree

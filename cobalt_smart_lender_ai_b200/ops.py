@@ -216,6 +216,13 @@ def partition_stable(bins, seg: torch.Tensor, feature: int, split_bin: int, defa
     return out, int(nl.item())
 
 
+def leaf_update(margin: torch.Tensor, rows: torch.Tensor | None, leaf_value: float, count: int | None = None) -> None:
+    """K7 on one leaf's segment: margin[rows[i]] += leaf_value (in place)."""
+    _need_cuda(margin, rows)
+    cnt = int(count if count is not None else (margin.numel() if rows is None else rows.numel()))
+    check(_lib.load().cb_leaf_update(_ptr(margin), _ptr(rows), cnt, float(leaf_value), _stream()))
+
+
 def predict(X: torch.Tensor, nodes: torch.Tensor, tree_off: torch.Tensor, base_margin: float,
             want_margin: bool = False, want_proba: bool = True):
     """K8.  nodes: packed int64 [n_nodes]; tree_off: int32 [n_trees+1]."""

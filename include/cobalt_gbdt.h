@@ -162,6 +162,12 @@ int cb_partition_stable(const uint8_t* bins, int64_t ldb, const uint32_t* seg_in
                         int split_bin, int default_left, uint32_t* seg_out, int64_t* n_left, void* workspace,
                         size_t workspace_bytes, void* stream);
 
+/* ---- K7 leaf-value / prediction-cache update (R10), standalone form: margin[row_idx[i]] += leaf_value for the
+ * `count` rows of one leaf's segment (row_idx NULL: rows 0..count-1).  Replaces xgboost's UpdatePredictionCache
+ * inside fit (src/model_train_test/model_tree_train_test.py:118); the trainer does the same inside its partition
+ * and final-level kernels. */
+int cb_leaf_update(float* margin, const uint32_t* row_idx, int64_t count, float leaf_value, void* stream);
+
 /* ---- K8 batched ensemble traversal (R11).  Replaces Booster.predict behind
  * predict_proba (src/api/cobalt_fast_api.py:91, src/model_train_test/model_tree_train_test.py:171-172).
  * nodes: packed 8-byte nodes {f32 cond; u32 meta} (meta: bits 0-14 feature, bit 15 default_left,
@@ -188,7 +194,9 @@ int cb_predict_heap(const float* X, int64_t n_rows, int n_features, int64_t ldx,
  * +inf; code = number of thresholds <= x, 255 = missing; at most 254 thresholds per feature), and "x < t_k"
  * becomes "code <= k".
  * cb_predict_q8_plan: trees per shared-memory chunk and plane_base, the shared-window address the kernel's code
- * planes start at on this device (it goes into every node word and back into cb_predict_q8, which checks it).
+ * planes start at on this device (it goes into every node word and back into cb_predict_q8, which refuses a value
+ * that is not this device's with CB_ERR_INVALID).  The first call on a device runs a one-thread probe kernel and
+ * synchronises; it allocates nothing.
  * codes: u8 [n_rows][ldc] row major, ldc = 4 * odd >= n_features, 16-byte aligned.
  * forest: u32 [Tp][2 << depth] per tree in 1-based heap order: word 0 unused, words 1 .. 2^depth - 1 the nodes
  * = span << 16 | plane_base + (default_left * n_features + feature) * 128 with span = k (+1 when default_left;

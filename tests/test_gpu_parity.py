@@ -224,6 +224,43 @@ def test_partition_stable_bit_exact(ops, data, cnt):
         assert np.array_equal(got.cpu().numpy().view(np.uint32), want)
 
 
+def test_leaf_update_standalone(ops):
+    """K7 as its own entry point: rows of a leaf's segment take the leaf value, one f32 add each (R10)."""
+    rng = np.random.default_rng(4)
+    m = rng.normal(size=5000).astype(np.float32)
+    rows = rng.permutation(5000)[:1777].astype(np.uint32)
+    leaf = np.float32(-0.123456789)
+    md = _dev(m.copy())
+    ops.leaf_update(md, _dev(rows.view(np.int32)), float(leaf))
+    want = m.copy()
+    want[rows] = want[rows] + leaf
+    assert np.array_equal(md.cpu().numpy().view(np.uint32), want.view(np.uint32))
+    ops.leaf_update(md, None, 0.5, count=100)                     # identity segment: rows 0..99
+    want[:100] = want[:100] + np.float32(0.5)
+    assert np.array_equal(md.cpu().numpy().view(np.uint32), want.view(np.uint32))
+    ops.leaf_update(md, None, 1.0, count=0)                       # empty segment is a no-op
+    assert np.array_equal(md.cpu().numpy().view(np.uint32), want.view(np.uint32))
+
+
+def test_predict_q8_refuses_a_foreign_plane_base(ops, fixture_forest):
+    """A forest laid out for another shared-memory window is refused with a status (no trap, the context survives)."""
+    import ctypes as C
+
+    from cobalt_smart_lender_ai_b200 import _lib
+    chunk, base = ops.predict_q8_plan(20, 7)
+    assert chunk >= 8
+    lib = _lib.load()
+    ldc = ops.q8_ldc(20)
+    codes = torch.zeros((128, ldc), dtype=torch.uint8, device="cuda")
+    forest = torch.zeros((chunk, 2 << 7), dtype=torch.int32, device="cuda")
+    out = torch.zeros(128, dtype=torch.float32, device="cuda")
+    rc = lib.cb_predict_q8(C.c_void_p(codes.data_ptr()), 128, 20, ldc, C.c_void_p(forest.data_ptr()), chunk, 7, 0.0,
+                           base + 128, C.c_void_p(out.data_ptr()), None, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == -1 and b"plane_base" in lib.cb_last_error()
+    torch.cuda.synchronize()                                      # still a healthy context
+    assert float(out.sum()) == 0.0
+
+
 def _block_major(b):
     """[n][ldb] row-major -> the library's column-block-major storage (same shape, different byte order)."""
     n, ldb = b.shape
