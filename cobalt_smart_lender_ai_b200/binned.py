@@ -26,8 +26,9 @@ MAX_CANDIDATES = 64
 
 
 def _all_reduce_sum(t: torch.Tensor) -> None:
-    d = torch.distributed
-    if d.is_available() and d.is_initialized() and d.get_world_size() > 1:
+    from . import parallel
+    d = parallel._dist()
+    if d is not None:
         d.all_reduce(t)
 
 

@@ -9,6 +9,12 @@ boosting rounds on the resident bins followed by a device-resident scoring pass.
 are the ones sklearn's class would produce (same ``ParameterSampler``, same splitter, same scorer input), so
 ``cv_results_['mean_test_score']``, ``best_params_`` and ``best_score_`` are identical (checked in
 tests/test_gpu_parity.py).  Anything else -- another estimator, another scorer, ``fit_params`` -- goes to sklearn's class.
+
+With one process per GPU (``torch.distributed`` initialised, every process holding the same X and y) the fold x
+candidate grid is dealt over the ranks: each rank runs WHOLE fits on its own GPU (``parallel.local_only``: no
+collective inside a fit), the score matrix is summed over ranks at the end, and every rank refits the winner -- the
+reference's ``n_jobs=-1`` process fan-out (:155) with GPUs in place of CPU workers.  Scores are bit-identical to the
+single-GPU run because every fit is the same single-GPU fit.
 """
 from __future__ import annotations
 
@@ -22,6 +28,7 @@ from sklearn.model_selection import RandomizedSearchCV as _SkRandomizedSearchCV
 from sklearn.model_selection import check_cv
 from sklearn.utils import _safe_indexing
 
+from . import parallel
 from .booster import Booster
 from .sklearn import XGBClassifier, _as_matrix, _to_device
 
@@ -63,26 +70,42 @@ class RandomizedSearchCV(MetaEstimatorMixin, BaseEstimator):
         candidates = list(ParameterSampler(self.param_distributions, self.n_iter, random_state=self.random_state))
         scores = np.zeros((len(candidates), len(splits)), np.float64)
         prepared = 0
-        for k, (train, test) in enumerate(splits):
-            X_tr, y_tr = _safe_indexing(X, train), _safe_indexing(y, train)
-            X_te, y_te = _safe_indexing(X, test), np.asarray(_safe_indexing(y, test))
-            ctxs: dict = {}                                  # one prepared fold per distinct (max_bin, spw, ...) setting
-            Xte_d = None
-            for ci, params in enumerate(candidates):
-                est = clone(self.estimator).set_params(**params)
-                key = tuple(repr(getattr(est, a)) for a in _PREPARE_KEYS)
-                if key not in ctxs:
-                    ctxs[key] = est._prepare(X_tr, y_tr)
-                    prepared += 1
-                c = ctxs[key]
-                forest = est._boost(c)
-                booster = Booster(forest, c["f"], c["names"], c["base_score"])
-                with torch.cuda.device(c["dev"]):
-                    if Xte_d is None:
-                        Xte_d = _to_device(_as_matrix(X_te)[0], c["dev"])
-                    proba = booster.predict_device(Xte_d).cpu().numpy()
-                scores[ci, k] = roc_auc_score(y_te, proba)   # what the 'roc_auc' scorer computes from predict_proba[:, 1]
-            del ctxs, Xte_d
+        d = parallel._dist()
+        world, rank = (d.get_world_size(), d.get_rank()) if d is not None else (1, 0)
+        # jobs in (fold, candidate) order, dealt in contiguous runs: a rank touches as few folds as possible
+        jobs = [(k, ci) for k in range(len(splits)) for ci in range(len(candidates))]
+        lo, hi = parallel.shard_rows(len(jobs), rank, world)
+        mine = jobs[lo:hi]
+        with parallel.local_only():
+            for k, (train, test) in enumerate(splits):
+                todo = [ci for kk, ci in mine if kk == k]
+                if not todo:
+                    continue
+                X_tr, y_tr = _safe_indexing(X, train), _safe_indexing(y, train)
+                X_te, y_te = _safe_indexing(X, test), np.asarray(_safe_indexing(y, test))
+                ctxs: dict = {}                                  # one prepared fold per distinct (max_bin, spw, ...) setting
+                Xte_d = None
+                for ci in todo:
+                    est = clone(self.estimator).set_params(**candidates[ci])
+                    key = tuple(repr(getattr(est, a)) for a in _PREPARE_KEYS)
+                    if key not in ctxs:
+                        ctxs[key] = est._prepare(X_tr, y_tr)
+                        prepared += 1
+                    c = ctxs[key]
+                    forest = est._boost(c)
+                    booster = Booster(forest, c["f"], c["names"], c["base_score"])
+                    with torch.cuda.device(c["dev"]):
+                        if Xte_d is None:
+                            Xte_d = _to_device(_as_matrix(X_te)[0], c["dev"])
+                        proba = booster.predict_device(Xte_d).cpu().numpy()
+                    scores[ci, k] = roc_auc_score(y_te, proba)   # what the 'roc_auc' scorer computes from predict_proba[:, 1]
+                del ctxs, Xte_d
+        if d is not None:                                        # every job ran on exactly one rank: the sum assembles the matrix
+            dev = self.estimator._cuda_device() if d.get_backend() == "nccl" else "cpu"
+            t = torch.from_numpy(scores).to(dev)
+            d.all_reduce(t)
+            scores = t.cpu().numpy()
+        self.jobs_per_rank_ = len(mine)
         mean = scores.mean(axis=1)
         rank = np.asarray(rankdata(-mean, method="min"), dtype=np.int32)
         self.cv_results_ = {"params": candidates, "mean_test_score": mean, "std_test_score": scores.std(axis=1),
@@ -100,7 +123,8 @@ class RandomizedSearchCV(MetaEstimatorMixin, BaseEstimator):
         self.n_splits_ = len(splits)
         self.prepared_folds_ = prepared
         if self.refit:
-            self.best_estimator_ = clone(self.estimator).set_params(**self.best_params_).fit(X, y)
+            with parallel.local_only():                          # every rank keeps its own copy of the winner
+                self.best_estimator_ = clone(self.estimator).set_params(**self.best_params_).fit(X, y)
         return self
 
     def predict(self, X):

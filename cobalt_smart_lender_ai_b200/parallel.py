@@ -12,9 +12,35 @@ import torch
 from . import ops
 
 
+_LOCAL_ONLY = 0
+
+
+class local_only:
+    """Inside this context a process ignores its process group: fits use this GPU's rows alone and exchange nothing.
+    It is how a job made of many independent fits (the tuning step's fold x candidate grid, reference
+    src/model_train_test/model_tree_train_test.py:148-159) puts ONE whole fit on each GPU instead of sharding every
+    fit over all of them."""
+
+    def __enter__(self):
+        global _LOCAL_ONLY
+        _LOCAL_ONLY += 1
+        return self
+
+    def __exit__(self, *a):
+        global _LOCAL_ONLY
+        _LOCAL_ONLY -= 1
+
+
 def _dist():
     d = torch.distributed
+    if _LOCAL_ONLY:
+        return None
     return d if d.is_available() and d.is_initialized() and d.get_world_size() > 1 else None
+
+
+def world_size() -> int:
+    d = _dist()
+    return d.get_world_size() if d is not None else 1
 
 
 def shard_rows(n_total: int, rank: int, world: int) -> tuple[int, int]:

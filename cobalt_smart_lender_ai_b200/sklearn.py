@@ -169,9 +169,8 @@ class XGBClassifier(ClassifierMixin, BaseEstimator):
         n, f = Xa.shape
         spw = float(self.scale_pos_weight)
 
-        dist = torch.distributed
-        world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
         from . import parallel
+        world = parallel.world_size()
         with torch.cuda.device(dev):
             Xd = _to_device(Xa, dev)
             yd = _to_device(y_u8, dev)

@@ -43,7 +43,8 @@ class GpuTrainer:
         self.lib = _lib.load()
         self.dev = bins.device
         self.group, self.world = None, 1
-        if group is not False and torch.distributed.is_available() and torch.distributed.is_initialized():
+        from . import parallel
+        if group is not False and parallel._dist() is not None:
             w = torch.distributed.get_world_size(group)
             if w > 1:
                 self.world, self.group = w, group

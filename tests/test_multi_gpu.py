@@ -22,3 +22,17 @@ def test_sharded_training_matches_oracle(world):
     sys.stdout.write(res.stdout[-3000:])
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert res.stdout.count("-> OK") == 6
+
+
+def test_search_grid_dealt_over_gpus_matches_one_gpu():
+    """SURVEY 8f-4, second half: one whole fit per GPU for the tuning step's fold x candidate grid."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    world = min(4, torch.cuda.device_count())
+    here = os.path.dirname(os.path.abspath(__file__))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr",
+           "127.0.0.1", "--master-port", "29561", os.path.join(here, "_mgpu_search_worker.py")]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    sys.stdout.write(res.stdout[-2000:])
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "-> OK" in res.stdout
