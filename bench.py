@@ -125,7 +125,10 @@ def _dist_init(n_gpus: int):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
         torch.cuda.set_device(local)
-        torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        # a short watchdog: a desynchronised run must end in minutes, not after the default 10-minute collective timeout
+        torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local),
+                                             timeout=datetime.timedelta(seconds=90))
     else:
         torch.cuda.set_device(0)
     return world, rank, local
@@ -335,30 +338,38 @@ def run_ours(args):
     rounds_per_s = args.steps / (ms / 1e3)
 
     # ---- roofline of the dominant kernel (hist_accum): CUDA events inside the library around every launch
-    lib.cb_trainer_enable_timing(tr.handle, 1)
+    graph_state = {"captured": bool(tr._graphs and all(g is not None for g in tr._graphs.values())), "error": tr.graph_error}
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     acc_ms = red_ms = 0.0
     per_level = {}
     alg_bytes = 0
     n_launch = 0
-    for _ in range(3):
-        _lib.check(lib.cb_trainer_round_begin(tr.handle, tr.n_trees, None, st))
-        for level in range(DEPTH):
-            _lib.check(lib.cb_trainer_level_hist(tr.handle, level, st))
-            a, r_, rows, nb = C.c_float(), C.c_float(), C.c_int64(), C.c_int()
-            _lib.check(lib.cb_trainer_last_hist_timing_sync(tr.handle, C.byref(a), C.byref(r_), C.byref(rows), C.byref(nb)))
-            if world > 1:
-                torch.distributed.all_reduce(tr._level_view(level), group=tr.group)
-            _lib.check(lib.cb_trainer_level_split(tr.handle, level, st))
-            acc_ms += a.value; red_ms += r_.value; n_launch += 1
-            per_level.setdefault(level, []).append((int(rows.value), int(nb.value), round(a.value * 1e3, 1)))
-            # R*(F + 8 + 4) + nodes_built*S*16 (S = total bins of the layout, not F*256);
-            # the row-index term is 0 at the root
-            alg_bytes += rows.value * (N_FEAT + 8 + (0 if level == 0 else 4)) + nb.value * S * 16
-        _lib.check(lib.cb_trainer_round_end(tr.handle, st))
-        tr.n_trees += 1
-    torch.cuda.synchronize()
-    lib.cb_trainer_enable_timing(tr.handle, 0)
+    # stepping a round level by level with a host synchronisation in between is only possible when the ranks meet in a
+    # host-issued collective (NCCL); with the exchange fused into the kernels (peer mode) a rank that waits on the host
+    # would leave its peers spinning on the device, so that mode reports no per-launch timing
+    if not tr.peer_mode:
+        lib.cb_trainer_enable_timing(tr.handle, 1)
+        for _ in range(3):
+            _lib.check(lib.cb_trainer_round_begin(tr.handle, tr.n_trees, None, st))
+            for level in range(DEPTH):
+                _lib.check(lib.cb_trainer_level_hist(tr.handle, level, st))
+                a, r_, rows, nb = C.c_float(), C.c_float(), C.c_int64(), C.c_int()
+                _lib.check(lib.cb_trainer_last_hist_timing_sync(tr.handle, C.byref(a), C.byref(r_), C.byref(rows), C.byref(nb)))
+                if world > 1:
+                    torch.distributed.all_reduce(tr._level_view(level), group=tr.group)
+                _lib.check(lib.cb_trainer_level_split(tr.handle, level, st))
+                acc_ms += a.value; red_ms += r_.value; n_launch += 1
+                per_level.setdefault(level, []).append((int(rows.value), int(nb.value), round(a.value * 1e3, 1)))
+                # R*(F + 8 + 4) + nodes_built*S*16 (S = total bins of the layout, not F*256);
+                # the row-index term is 0 at the root
+                alg_bytes += rows.value * (N_FEAT + 8 + (0 if level == 0 else 4)) + nb.value * S * 16
+            _lib.check(lib.cb_trainer_round_end(tr.handle, st))
+            tr.n_trees += 1
+        torch.cuda.synchronize()
+        lib.cb_trainer_enable_timing(tr.handle, 0)
+    timed_launches = n_launch > 0
+    if not timed_launches:
+        acc_ms, n_launch, alg_bytes = 1.0, 1, 0
     achieved = alg_bytes / (acc_ms / 1e3) / 1e9
     traffic, traffic_src = None, None
     try:      # per-launch DRAM bytes of the same kernel from the committed ncu --set full capture
@@ -376,6 +387,10 @@ def run_ours(args):
                 "alg_bytes_per_launch": int(alg_bytes / n_launch), "hist_reduce_ms_per_launch": round(red_ms / n_launch, 4),
                 "hist_share_of_round": round((acc_ms + red_ms) / 3 / (ms / args.steps), 3),
                 "per_level_rows_nodes_us": {str(k): v[-1] for k, v in per_level.items()}}
+    if not timed_launches:
+        roofline = {"kernel": roofline["kernel"], "bound": "hbm", "achieved": None, "peak": peak, "unit": "GB/s", "frac": None,
+                    "traffic": None, "note": "no per-launch timing in peer mode (the exchange is inside the kernels; a host "
+                    "synchronisation between the halves of a level would stall the peers)"}
     auc = None
     try:
         from sklearn.metrics import roc_auc_score
@@ -556,7 +571,7 @@ def run_ours(args):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4),
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int64 fixed-point (f32 gradients, f64 gains)",
                 "data": "synthetic", "config": _config(n_rows, args.steps, args.warmup, world),
-                "detail": {"total_bins": S, "effective_bins_per_feature": 255, "layout": layout,
+                "detail": {"total_bins": S, "effective_bins_per_feature": 255, "layout": layout, "cuda_graph": graph_state,
                            "exchange": ("NVLink peer memory inside the split scan" if peer_mode else "NCCL allreduce") if world > 1 else None},
                 "roofline": roofline, "cpu_baseline": cpu, "cpu_baseline_hgb": hgb, "parity": parity, "c0": c0,
                 "e2e": e2e, "gpu_launches": int(launches),
