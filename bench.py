@@ -13,6 +13,7 @@ all-reduced over NCCL.  One JSON line is printed by rank 0.  See DESIGN.md "meas
 from __future__ import annotations
 
 import argparse
+import contextlib
 import json
 import os
 import subprocess
@@ -47,8 +48,9 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
     NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, index: int):
+    def __init__(self, index: int, period_s: float = 0.002):
         self.samples, self.proc, self.index, self.nv, self.h, self.source = [], None, index, None, None, None
+        self.period = period_s
         self._stop = threading.Event()
         try:
             import pynvml
@@ -72,7 +74,7 @@ class ClockSampler:
                 self.samples.append((mhz, self.max_mhz, [bool(r & b) for b in bits]))
             except Exception:
                 pass
-            self._stop.wait(0.002)
+            self._stop.wait(self.period)
 
     def _poll_smi(self):
         for l in self.proc.stdout:
@@ -332,7 +334,8 @@ def run_ours(args):
                     sg=sg, sh=sh, max_trees=total_rounds, row_offset=r0)
     tr.boost(args.warmup)
     l0 = tr.launch_count()
-    with ClockSampler(dev.index or 0) as clk:
+    # NVML calls take a driver-wide lock: with one process per GPU only rank 0 samples, and less often
+    with (ClockSampler(dev.index or 0, 0.002 if world == 1 else 0.01) if rank == 0 else contextlib.nullcontext()) as clk:
         ms = _timed(lambda: tr.boost(args.steps), world, dev)
     launches = tr.launch_count() - l0
     rounds_per_s = args.steps / (ms / 1e3)

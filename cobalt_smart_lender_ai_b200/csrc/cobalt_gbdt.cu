@@ -33,37 +33,15 @@ static bool pdl_enabled() {     // measured on B200: 5 % slower with the overlap
   static const bool on = [] { const char* e = getenv("COBALT_PDL"); return e && e[0] == '1'; }();
   return on;
 }
-// L2 residency hint of a launch: accesses inside [base, base + bytes) are kept as persisting lines (the per-row state
-// that every level gathers from: gradient pairs, row order, margins), everything else streams through.
-struct L2Window { const void* base = nullptr; size_t bytes = 0; };
-static thread_local L2Window g_l2_window;      // set by the trainer around its launches; empty = no hint
-struct L2Scope {
-  explicit L2Scope(const L2Window& w) { g_l2_window = w; }
-  ~L2Scope() { g_l2_window = L2Window(); }
-};
-
 template <typename... P, typename... A>
 static inline cudaError_t launch_dep(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, A&&... args) {
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof cfg);
   cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
-  cudaLaunchAttribute at[2];
-  int na = 0;
-  if (pdl_enabled()) {
-    at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[na].val.programmaticStreamSerializationAllowed = 1;
-    ++na;
-  }
-  if (g_l2_window.bytes) {
-    at[na].id = cudaLaunchAttributeAccessPolicyWindow;
-    at[na].val.accessPolicyWindow.base_ptr = const_cast<void*>(g_l2_window.base);
-    at[na].val.accessPolicyWindow.num_bytes = g_l2_window.bytes;
-    at[na].val.accessPolicyWindow.hitRatio = 1.0f;
-    at[na].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-    at[na].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-    ++na;
-  }
-  cfg.attrs = at; cfg.numAttrs = na;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kern, static_cast<P>(std::forward<A>(args))...);
 }
 
@@ -707,7 +685,6 @@ struct cb_trainer_s {
   // conflict-free histogram path
   bool cf;
   int cf_R, cf_smem;
-  L2Window win_rows, win_margin;   // persisting-L2 hints: [gpair | row order x 2] for the level kernels, margins for grad / final apply
   CfLayout* cf_lay;
   int32_t* cf_slot_of;
   int32_t* cf_fold_src;
@@ -832,23 +809,6 @@ int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, v
     t->res_scatter = std::max(2, b * t->di.sm_count);
     t->res_final = std::max(2, c * t->di.sm_count);
   }
-  {
-    // per-row state that every level gathers from stays in L2 (it is 44 MB at 2.2M rows; the binned matrix streams past it)
-    int max_persist = 0, max_win = 0;
-    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, di.device);
-    cudaDeviceGetAttribute(&max_win, cudaDevAttrMaxAccessPolicyWindowSize, di.device);
-    const char* env = getenv("COBALT_L2_PERSIST");
-    const size_t rows_bytes = (size_t)(reinterpret_cast<char*>(t->rows[1] + cfg->n_rows) - reinterpret_cast<char*>(t->gpair));
-    const size_t margin_bytes = (size_t)cfg->n_rows * sizeof(float);
-    if (!(env && env[0] == '0') && max_persist > 0 && max_win > 0 && rows_bytes + margin_bytes <= (size_t)max_persist &&
-        rows_bytes <= (size_t)max_win) {
-      if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, rows_bytes + margin_bytes) == cudaSuccess) {
-        t->win_rows.base = t->gpair; t->win_rows.bytes = rows_bytes;
-        t->win_margin.base = buf->margin; t->win_margin.bytes = margin_bytes;
-      }
-      cudaGetLastError();
-    }
-  }
   t->cur = 0; t->identity = true; t->tree_index = 0; t->fmask = nullptr; t->launches = 0; t->timing = false; t->profiling = false; t->n_marks = 0;
   memset(&t->pc, 0, sizeof t->pc); t->pc.world = 1;
   plan_tiles_kernel<<<1, 1>>>(buf->bin_ptr, cfg->n_features, budget, t->plan);
@@ -925,7 +885,6 @@ int cb_trainer_create(const cb_train_config* cfg, const cb_train_buffers* buf, v
 }
 
 void cb_trainer_destroy(cb_trainer* tr) {
-  if (tr && tr->win_rows.bytes) cudaCtxResetPersistingL2Cache();   // hand the set-aside lines back
   if (tr && tr->timing)
     for (int i = 0; i < 3; ++i) cudaEventDestroy(tr->ev[i]);
   delete tr;
@@ -1010,7 +969,6 @@ int cb_trainer_round_begin(cb_trainer* t, int tree_index, const uint8_t* feature
   }
   mark(t, s, "start");
   int g = (int)std::min<int64_t>(ceil_div(n, 256), (int64_t)t->di.sm_count * 8);
-  L2Scope l2(t->win_rows);                   // the gradient pairs it writes are what every level gathers from
   // root_tot is zero here: init_state_kernel / the previous round's round_end_kernel cleared it
   CB_CUDA(launch_dep(grad_kernel, dim3(g), dim3(256), 0, s, t->buf.margin, t->buf.y, t->buf.weight, n, t->cfg.scale_pos_weight,
                      ldexpf(1.0f, t->cfg.tree.sg), ldexpf(1.0f, t->cfg.tree.sh), t->cfg.keep_thresh, t->cfg.seed, 0u,
@@ -1029,7 +987,6 @@ int cb_trainer_level_hist(cb_trainer* t, int level, void* stream) {
   if (!t || level < 0 || level >= t->cfg.tree.max_depth) return fail(CB_ERR_INVALID, "trainer: bad level");
   cudaStream_t s = (cudaStream_t)stream;
   const int nb = level == 0 ? 1 : (1 << (level - 1));
-  L2Scope l2(t->win_rows);
   if (t->cf) {
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
     const BinsView bv = make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked);
@@ -1102,7 +1059,6 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   const BinsView view = make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked);
   const uint32_t* rin = t->rows[t->cur];
   const int ident = t->identity ? 1 : 0;
-  L2Scope l2(level + 1 < D ? t->win_rows : t->win_margin);
   if (level + 1 < D) {
     uint32_t* rout = t->rows[t->cur ^ 1];
     const int pgrid = std::min(t->n_part_tiles, t->res_flags - 1) + 1;

@@ -40,7 +40,7 @@ def timed(fn, reps=3):
     return e0.elapsed_time(e1) / reps
 
 
-t_bin0 = timed(lambda: _lib.check(lib.cb_bin_pack_u8(X.data_ptr(), n, f, f, cuts.data_ptr(), n_cuts.data_ptr(), None,
+t_bin0 = timed(lambda: _lib.check(lib.cb_bin_pack_u8(X.data_ptr(), n, f, f, cuts.data_ptr(), n_cuts.data_ptr(), None, None, None,
                                                      codes.data_ptr(), ldc, 0, st)))
 ref = codes.clone()
 codes.zero_()
