@@ -374,17 +374,20 @@ def run_ours(args):
     if not timed_launches:
         acc_ms, n_launch, alg_bytes = 1.0, 1, 0
     achieved = alg_bytes / (acc_ms / 1e3) / 1e9
-    traffic, traffic_src = None, None
+    traffic, traffic_src, traffic_ratio = None, None, None
     try:      # per-launch DRAM bytes of the same kernel from the committed ncu --set full capture
         rf = [f for f in ("r02_roofline.json", "r01_roofline.json") if os.path.exists(os.path.join(ROOT, "profiles", f))][0]
         with open(os.path.join(ROOT, "profiles", rf)) as fh:
-            traffic = int(json.load(fh)["dram_bytes_per_launch_mean"]) if world == 1 else None
-        traffic_src = f"profiles/{rf} (ncu --set full capture of the same command, committed)"
+            rfj = json.load(fh)
+        traffic = int(rfj["dram_bytes_per_launch_mean"]) if world == 1 else None
+        traffic_ratio = rfj.get("traffic_over_algorithmic")
+        traffic_src = (f"profiles/{rf}: ncu --set full capture of this command's histogram launches (committed); its own "
+                       f"launches' DRAM bytes / algorithmic bytes = {traffic_ratio}")
     except Exception:
         pass
     roofline = {"kernel": "hist_accum_cf_kernel" if cf_flag else "hist_accum_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
                 "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src,
-                "peak_source": peak_src,
+                "traffic_over_algorithmic_in_capture": traffic_ratio, "peak_source": peak_src,
                 "frac_accum_plus_reduce": round(alg_bytes / ((acc_ms + red_ms) / 1e3) / 1e9 / peak, 4),
                 "avg_launch_ms": round(acc_ms / n_launch, 4), "launches_timed": n_launch,
                 "alg_bytes_per_launch": int(alg_bytes / n_launch), "hist_reduce_ms_per_launch": round(red_ms / n_launch, 4),

@@ -18,7 +18,7 @@ from cobalt_smart_lender_ai_b200.synth import make_lending  # noqa: E402
 def main():
     local = int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
-    torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=__import__("datetime").timedelta(seconds=120))
     rank, world = torch.distributed.get_rank(), torch.distributed.get_world_size()
     X, y, _ = make_lending(30000, 24, seed=21)
     X, y = X.numpy(), y.numpy().astype(int)

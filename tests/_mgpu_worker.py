@@ -17,7 +17,7 @@ from oracle import oracle as O  # noqa: E402
 def main():
     local = int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
-    torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=__import__("datetime").timedelta(seconds=120))
     rank, world = torch.distributed.get_rank(), torch.distributed.get_world_size()
     ok = True
     for n, f, depth, trees in ((40000, 150, 6, 6), (9001, 37, 4, 5), (5003, 5, 3, 3)):   # last: fewer features than ranks at world 8

@@ -90,9 +90,17 @@ def full(rep, tag):
     hist = [r for r in rows if "hist_accum" in r[idx["Kernel Name"]]]
     if hist:
         tr = [num(r, "dram__bytes_read.sum") + num(r, "dram__bytes_write.sum") for r in hist]
+        # rows a launch scanned = shared-memory atomic warp instructions / 8 (4 code bytes x (g, h) per row word);
+        # algorithmic bytes of the SAME launches by SURVEY 8d's formula R * (F + 8 + 4 [below the root]) with F = 150
+        rows_ = [num(r, "smsp__inst_executed_op_shared_atom.sum") / 8 for r in hist]
+        alg = [x * (150 + 8 + (0 if "1>" in r[idx["Kernel Name"]].split("(")[0] else 4)) for x, r in zip(rows_, hist)]
         js = {"kernel": "hist_accum_cf_kernel", "launches_captured": len(hist),
               "dram_bytes_per_launch": [int(x) for x in tr], "dram_bytes_per_launch_mean": int(sum(tr) / len(tr)),
-              "note": "one ncu --set full capture of consecutive launches (levels 0.. of one round); dram__bytes_read.sum + dram__bytes_write.sum"}
+              "rows_per_launch": [int(x) for x in rows_], "algorithmic_bytes_per_launch": [int(x) for x in alg],
+              "traffic_over_algorithmic": round(sum(tr) / sum(alg), 3),
+              "note": "one ncu --set full capture of consecutive launches (levels 0.. of one round); dram__bytes_read.sum + "
+                      "dram__bytes_write.sum; rows from the launch's shared-atomic instruction count (layout: 128-byte rows, "
+                      "one-hot groups packed), histogram write-out not counted"}
         with open(os.path.join(ROOT, "profiles", f"{tag}_roofline.json"), "w") as fh:
             json.dump(js, fh, indent=1)
         print("hist traffic per launch (MB):", [round(x / 1e6, 1) for x in tr])

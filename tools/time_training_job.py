@@ -30,7 +30,7 @@ world = int(os.environ.get("WORLD_SIZE", "1"))
 local = int(os.environ.get("LOCAL_RANK", "0"))
 torch.cuda.set_device(local)
 if world > 1:
-    torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=__import__("datetime").timedelta(seconds=120))
 rank = int(os.environ.get("RANK", "0"))
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 2_200_000
 f = int(sys.argv[2]) if len(sys.argv) > 2 else 104
