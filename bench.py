@@ -335,7 +335,7 @@ def run_ours(args):
     tr.boost(args.warmup)
     l0 = tr.launch_count()
     # NVML calls take a driver-wide lock: with one process per GPU only rank 0 samples, and less often
-    with (ClockSampler(dev.index or 0, 0.002 if world == 1 else 0.01) if rank == 0 else contextlib.nullcontext()) as clk:
+    with (ClockSampler(dev.index or 0, 0.002 if world == 1 else 0.004) if rank == 0 else contextlib.nullcontext()) as clk:
         ms = _timed(lambda: tr.boost(args.steps), world, dev)
     launches = tr.launch_count() - l0
     rounds_per_s = args.steps / (ms / 1e3)

@@ -110,6 +110,8 @@ _SIGS = {
     "cb_sigmoid": (C.c_int, [_VP, _I64, _VP, _VP]),
     "cb_hist_workspace_bytes": (C.c_int, [_I64, _I, C.POINTER(_SZ)]),
     "cb_hist_build": (C.c_int, [_VP, _I64, _I, _VP, _VP, _I64, _VP, _I, _VP, _VP, _SZ, _VP]),
+    "cb_hist_build_cf_workspace_bytes": (C.c_int, [_I64, _I, C.POINTER(_SZ)]),
+    "cb_hist_build_cf_sync": (C.c_int, [_VP, _I64, _I64, _I, _VP, _VP, _VP, _I, _I, _VP, _VP, _I64, _VP, _I, _VP, _VP, _SZ, _VP]),
     "cb_hist_subtract": (C.c_int, [_VP, _VP, _VP, _I64, _VP]),
     "cb_split_scan_workspace_bytes": (C.c_int, [_I, C.POINTER(_SZ)]),
     "cb_split_scan": (C.c_int, [_VP, _VP, _I, _VP, _VP, _VP, C.POINTER(TreeParams), _VP, _VP, _VP, _SZ, _VP]),

@@ -3,6 +3,8 @@
 #include <mutex>
 #include <new>
 
+#include <nvtx3/nvToolsExt.h>   // header-only; a no-op unless a profiler is attached
+
 #include "sketch.cuh"
 #include "hist_cf.cuh"
 #include "trainer.cuh"
@@ -25,6 +27,13 @@ int device_info(DeviceInfo* out) {
 }
 
 static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+// NVTX range around the launches of one stage of the path (sketch / bin / grad / hist / scan+partition / leaf /
+// predict): Nsight Systems then shows the stages -- and the all-reduce between "hist" and "split" -- by name.
+struct StageRange {
+  explicit StageRange(const char* name) { nvtxRangePushA(name); }
+  ~StageRange() { nvtxRangePop(); }
+};
 
 // Launch with programmatic stream serialisation (common.cuh pdl_enter): the kernel may be scheduled while its
 // predecessor in the stream is still draining; it blocks in griddepcontrol.wait until that one has completed.
@@ -145,6 +154,7 @@ int cb_bin_pack_u8(const float* X, int64_t n, int f, int64_t ldx, const float* c
       ((grp_ptr == nullptr) != (grp_feat == nullptr)))
     return fail(CB_ERR_INVALID, "cb_bin_pack_u8: bad arguments (ldb must be a multiple of 4 and hold every column)");
   if (n == 0) return CB_OK;
+  StageRange nv("cobalt:bin_pack");
   int wpr = (int)(ldb / 4);
   int64_t items = n * wpr;
   bin_pack_kernel<<<ceil_div(items, 256), 256, 0, (cudaStream_t)stream>>>(X, n, f, ldx, cuts, n_cuts, pos_feature, grp_ptr, grp_feat,
@@ -229,6 +239,126 @@ int cb_hist_build(const uint8_t* bins, int64_t ldb, int f, const int32_t* gpair,
   if (rc) return rc;
   hist_reduce_kernel<<<dim3(ceil_div(total_bins, 256), 1), 256, 0, s>>>(partials, plan, total_bins, hist);
   CB_LAUNCH_CHECK();
+  return CB_OK;
+}
+
+// ---- K4 through the conflict-free kernel, standalone (the kernel the trainer runs at every level)
+}  // extern "C"
+namespace cb {
+__global__ void __launch_bounds__(256) sum_gpair_kernel(const int2* __restrict__ gpair, const uint32_t* __restrict__ rows,
+                                                        int64_t count, unsigned long long* __restrict__ totals) {
+  long long g = 0, h = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
+    const int2 q = gpair[rows ? (int64_t)rows[i] : i];
+    g += q.x; h += q.y;
+  }
+  g = warp_sum_i64(g); h = warp_sum_i64(h);
+  if ((threadIdx.x & 31) == 0) { atomicAdd(totals, (unsigned long long)g); atomicAdd(totals + 1, (unsigned long long)h); }
+}
+// members of a one-hot group column: bin 0 = node totals - bin 1 (what the trainer's split scan derives)
+__global__ void group_bin0_kernel(int64_t* __restrict__ hist, const int32_t* __restrict__ bin_ptr,
+                                  const int32_t* __restrict__ feat_code, int f, const long long* __restrict__ totals) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= f || feat_code[j] == 0) return;
+  const int b0 = bin_ptr[j];
+  hist[2 * (size_t)b0] = totals[0] - hist[2 * (size_t)(b0 + 1)];
+  hist[2 * (size_t)b0 + 1] = totals[1] - hist[2 * (size_t)(b0 + 1) + 1];
+}
+static size_t hist_cf_layout(int64_t max_rows, int f, const DeviceInfo& di, void* ws, HistPlan** plan, CfLayout** lay,
+                             int32_t** slot_of, int32_t** fsrc, int32_t** fdst, int32_t** feat_code, long long** totals,
+                             unsigned int** flag, int32_t** partials) {
+  Bump b(ws);
+  const int words = hist_budget_slots(di);              // upper bound of R * 32
+  HistPlan* p = b.take<HistPlan>(1);
+  CfLayout* l = b.take<CfLayout>(1);
+  int32_t* so = b.take<int32_t>((size_t)words);
+  int32_t* a = b.take<int32_t>((size_t)words);
+  int32_t* c = b.take<int32_t>((size_t)words);
+  int32_t* fc = b.take<int32_t>((size_t)f);
+  long long* t = b.take<long long>(2);
+  unsigned int* fl = b.take<unsigned int>(1);
+  int32_t* pa = b.take<int32_t>((size_t)max_partials(max_rows, di.sm_count) * 2 * words);
+  if (plan) { *plan = p; *lay = l; *slot_of = so; *fsrc = a; *fdst = c; *feat_code = fc; *totals = t; *flag = fl; *partials = pa; }
+  return b.used();
+}
+}  // namespace cb
+extern "C" {
+
+int cb_hist_build_cf_workspace_bytes(int64_t max_rows, int n_features, size_t* bytes) {
+  if (!bytes || max_rows < 0 || n_features <= 0) return fail(CB_ERR_INVALID, "cb_hist_build_cf_workspace_bytes: bad arguments");
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  *bytes = hist_cf_layout(max_rows, n_features, di, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+  return CB_OK;
+}
+
+int cb_hist_build_cf_sync(const uint8_t* bins, int64_t n_rows, int64_t ldb, int blocked, const int32_t* pos_feature,
+                          const int32_t* grp_ptr, const int32_t* grp_feat, int n_groups, int f, const int32_t* gpair,
+                          const uint32_t* row_idx, int64_t count, const int32_t* bin_ptr, int total_bins, int64_t* hist,
+                          void* ws, size_t ws_bytes, void* stream) {
+  if (!bins || !pos_feature || !gpair || !bin_ptr || !hist || !ws || f <= 0 || total_bins <= 0 || count < 0 || n_rows <= 0 ||
+      ldb <= 0 || (ldb & 3) || count > 2147483647LL || n_groups < 0 || (n_groups > 0 && (!grp_ptr || !grp_feat)))
+    return fail(CB_ERR_INVALID, "cb_hist_build_cf_sync: bad arguments");
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  size_t need = 0;
+  cb_hist_build_cf_workspace_bytes(count, f, &need);
+  if (ws_bytes < need) return fail(CB_ERR_WORKSPACE, "cb_hist_build_cf_sync: workspace %zu < %zu bytes", ws_bytes, need);
+  cudaStream_t s = (cudaStream_t)stream;
+  CB_CUDA(cudaStreamSynchronize(s));
+  std::vector<int32_t> bp((size_t)f + 1), pf((size_t)ldb), gptr((size_t)n_groups + 1, 0), gfeat, fc((size_t)f, 0);
+  CB_CUDA(cudaMemcpy(bp.data(), bin_ptr, sizeof(int32_t) * (f + 1), cudaMemcpyDeviceToHost));
+  CB_CUDA(cudaMemcpy(pf.data(), pos_feature, sizeof(int32_t) * ldb, cudaMemcpyDeviceToHost));
+  if (n_groups > 0) {
+    CB_CUDA(cudaMemcpy(gptr.data(), grp_ptr, sizeof(int32_t) * (n_groups + 1), cudaMemcpyDeviceToHost));
+    if (gptr[0] != 0 || gptr[n_groups] < n_groups || gptr[n_groups] > f) return fail(CB_ERR_INVALID, "cb_hist_build_cf_sync: grp_ptr is malformed");
+    gfeat.resize((size_t)gptr[n_groups]);
+    CB_CUDA(cudaMemcpy(gfeat.data(), grp_feat, sizeof(int32_t) * gfeat.size(), cudaMemcpyDeviceToHost));
+  }
+  if (bp[f] != total_bins) return fail(CB_ERR_INVALID, "cb_hist_build_cf_sync: total_bins does not match bin_ptr");
+  GroupTable gt;
+  gt.n_groups = n_groups; gt.ptr = gptr.data(); gt.feat = gfeat.data();
+  CfHostTables tb;
+  if (!build_cf_tables(bp.data(), pf.data(), f, gt, ldb, hist_budget_slots(di) * 8, &tb))
+    return fail(CB_ERR_UNSUPPORTED, "cb_hist_build_cf_sync: the placement has no conflict-free shared-memory image; use cb_hist_build");
+  const BinsView bv = make_view(bins, n_rows, ldb, blocked);
+  if (tb.lay.n_blocks > 1 && !bv.blocked) return fail(CB_ERR_UNSUPPORTED, "cb_hist_build_cf_sync: rows wider than 128 bytes must be stored block-major");
+  for (int g = 0; g < n_groups; ++g)
+    for (int k = gptr[g]; k < gptr[g + 1]; ++k) fc[gfeat[k]] = k - gptr[g] + 1;
+  HistPlan* plan; CfLayout* lay; int32_t *slot_of, *fsrc, *fdst, *feat_code, *partials; long long* totals; unsigned int* flag;
+  hist_cf_layout(count, f, di, ws, &plan, &lay, &slot_of, &fsrc, &fdst, &feat_code, &totals, &flag, &partials);
+  CB_CUDA(cudaMemsetAsync(plan, 0, sizeof(HistPlan), s));
+  CB_CUDA(cudaMemsetAsync(totals, 0, 2 * sizeof(long long), s));
+  CB_CUDA(cudaMemsetAsync(flag, 0, sizeof(unsigned int), s));
+  CB_CUDA(cudaMemcpyAsync(lay, &tb.lay, sizeof(CfLayout), cudaMemcpyHostToDevice, s));
+  CB_CUDA(cudaMemcpyAsync(slot_of, tb.slot_of.data(), sizeof(int32_t) * tb.slot_of.size(), cudaMemcpyHostToDevice, s));
+  if (tb.lay.n_fold) {
+    CB_CUDA(cudaMemcpyAsync(fsrc, tb.fold_src.data(), sizeof(int32_t) * tb.fold_src.size(), cudaMemcpyHostToDevice, s));
+    CB_CUDA(cudaMemcpyAsync(fdst, tb.fold_dst.data(), sizeof(int32_t) * tb.fold_dst.size(), cudaMemcpyHostToDevice, s));
+  }
+  CB_CUDA(cudaMemcpyAsync(feat_code, fc.data(), sizeof(int32_t) * f, cudaMemcpyHostToDevice, s));
+  CB_CUDA(cudaStreamSynchronize(s));                     // the host vectors go out of scope below
+  const int grid = std::min(di.sm_count, kMaxGrid);
+  plan_single_kernel<<<1, 1, 0, s>>>(plan, (int)count, grid);
+  CB_CUDA(cudaFuncSetAttribute(hist_accum_cf_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCfSmemBytes));
+  CB_CUDA(cudaFuncSetAttribute(hist_accum_cf_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCfSmemBytes));
+  auto kern = row_idx ? hist_accum_cf_kernel<4, false> : hist_accum_cf_kernel<4, true>;
+  kern<<<grid, 1024, kCfSmemBytes, s>>>(bins, bv.blocked ? n_rows : 0, bv.blocked ? bv.last_w : (int)ldb,
+                                        reinterpret_cast<const int2*>(gpair), row_idx, plan, lay, fsrc, fdst, partials, slot_of,
+                                        total_bins, hist, plan->done, flag, nullptr, nullptr);
+  if (n_groups > 0) {
+    if (count > 0)
+      sum_gpair_kernel<<<std::min(ceil_div(count, 256), di.sm_count * 4), 256, 0, s>>>(
+          reinterpret_cast<const int2*>(gpair), row_idx, count, reinterpret_cast<unsigned long long*>(totals));
+    group_bin0_kernel<<<ceil_div(f, 128), 128, 0, s>>>(hist, bin_ptr, feat_code, f, totals);
+  }
+  CB_LAUNCH_CHECK();
+  unsigned int timed_out = 0;
+  CB_CUDA(cudaMemcpyAsync(&timed_out, flag, sizeof timed_out, cudaMemcpyDeviceToHost, s));
+  CB_CUDA(cudaStreamSynchronize(s));
+  if (timed_out) return fail(CB_ERR_CUDA, "cb_hist_build_cf_sync: the CTAs of the launch were not co-resident (another kernel holds SMs)");
   return CB_OK;
 }
 
@@ -961,6 +1091,7 @@ int cb_trainer_round_begin(cb_trainer* t, int tree_index, const uint8_t* feature
   if (!t) return fail(CB_ERR_INVALID, "trainer: null handle");
   if (tree_index >= t->cfg.max_trees) return fail(CB_ERR_INVALID, "trainer: tree_index %d out of range", tree_index);
   cudaStream_t s = (cudaStream_t)stream;
+  StageRange nv("cobalt:grad");
   t->fmask = feature_masks; t->identity = true; t->cur = 0;
   const int64_t n = t->cfg.n_rows;
   if (tree_index >= 0) {                 // negative: keep the device-side counter (CUDA-graph replay)
@@ -987,6 +1118,7 @@ int cb_trainer_level_hist(cb_trainer* t, int level, void* stream) {
   if (!t || level < 0 || level >= t->cfg.tree.max_depth) return fail(CB_ERR_INVALID, "trainer: bad level");
   cudaStream_t s = (cudaStream_t)stream;
   const int nb = level == 0 ? 1 : (1 << (level - 1));
+  StageRange nv("cobalt:hist");
   if (t->cf) {
     if (t->timing) CB_CUDA(cudaEventRecord(t->ev[0], s));
     const BinsView bv = make_view(t->buf.bins, t->cfg.n_rows, t->cfg.ldb, t->cfg.blocked);
@@ -1039,6 +1171,7 @@ int cb_trainer_level_split(cb_trainer* t, int level, void* stream) {
   const int n = (int)t->cfg.n_rows;
   const int n_groups = ceil_div(t->n_part_tiles, kTileGroup);
   const int fx = t->pc.world > 1 ? t->pc.f1 - t->pc.f0 : t->cfg.n_features;   // peer mode: this rank's feature slice
+  StageRange nv(level + 1 < D ? "cobalt:scan+partition" : "cobalt:scan+leaf");
   {                                         // a rank whose slice is empty still needs the kernel's housekeeping CTA
     CB_CUDA(launch_dep(scan_level_fused_kernel, dim3(fx > 0 ? fx : 1, ln), dim3(128), 0, s,
                        t->level_buf, t->pool, t->plan, t->buf.bin_ptr, t->cfg.n_features, t->S, t->st, level, t->na, t->cfg.tree,

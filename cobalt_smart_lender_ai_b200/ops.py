@@ -80,8 +80,9 @@ def sketch_cuts(X: torch.Tensor, max_bin: int = 256):
     n_cuts = torch.empty(f, dtype=torch.int32, device=X.device)
     min_vals = torch.empty(f, dtype=torch.float32, device=X.device)
     wp, wb = _aligned(ws)
-    check(lib.cb_sketch_cuts(_ptr(X), n, f, _ld(X), max_bin, _ptr(cuts), _ptr(n_cuts), _ptr(min_vals), wp, wb,
-                             _stream()))
+    with torch.cuda.nvtx.range("cobalt:sketch"):
+        check(lib.cb_sketch_cuts(_ptr(X), n, f, _ld(X), max_bin, _ptr(cuts), _ptr(n_cuts), _ptr(min_vals), wp, wb,
+                                 _stream()))
     return cuts, n_cuts, min_vals
 
 
@@ -175,6 +176,22 @@ def hist_build(bins, n_features, gpair, row_idx, bin_ptr, total_bins, count=None
     wp, wb = _aligned(ws)
     check(lib.cb_hist_build(_ptr(bins), bins.stride(0), n_features, _ptr(gpair), _ptr(row_idx), cnt, _ptr(bin_ptr),
                             total_bins, _ptr(hist), wp, wb, _stream()))
+    return hist
+
+
+def hist_build_cf(bm, gpair, row_idx, bin_ptr, total_bins, count=None) -> torch.Tensor:
+    """K4 on one node through the conflict-free kernel the trainer uses.  bm: binned.BinnedMatrix.  int64 [total_bins, 2]."""
+    _need_cuda(bm.bins, gpair, bin_ptr)
+    lib = _lib.load()
+    cnt = int(count if count is not None else (bm.n_rows if row_idx is None else row_idx.numel()))
+    need = C.c_size_t()
+    check(lib.cb_hist_build_cf_workspace_bytes(cnt, bm.n_features, C.byref(need)))
+    ws = workspace(need.value, bm.bins.device)
+    hist = torch.zeros((total_bins, 2), dtype=torch.int64, device=bm.bins.device)
+    wp, wb = _aligned(ws)
+    check(lib.cb_hist_build_cf_sync(_ptr(bm.bins), bm.n_rows, bm.ldb, int(bm.blocked), _ptr(bm.pos), _ptr(bm.grp_ptr),
+                                    _ptr(bm.grp_feat), bm.n_groups, bm.n_features, _ptr(gpair), _ptr(row_idx), cnt,
+                                    _ptr(bin_ptr), total_bins, _ptr(hist), wp, wb, _stream()))
     return hist
 
 
@@ -285,6 +302,7 @@ def predict_q8(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, forest
     p = torch.empty(n, dtype=torch.float32, device=X.device) if want_proba else None
     lib = _lib.load()
     codes = torch.empty((min(n, batch_rows), ldc), dtype=torch.uint8, device=X.device)
+    torch.cuda.nvtx.range_push("cobalt:predict")
     for r0 in range(0, n, batch_rows):
         r1 = min(n, r0 + batch_rows)
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if events is not None else None
@@ -299,6 +317,7 @@ def predict_q8(X: torch.Tensor, cuts: torch.Tensor, n_cuts: torch.Tensor, forest
         if ev:
             ev[2].record()
             events.append(ev)
+    torch.cuda.nvtx.range_pop()
     return m, p
 
 

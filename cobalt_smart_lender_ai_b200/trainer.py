@@ -172,7 +172,8 @@ class GpuTrainer:
             check(self.lib.cb_trainer_round_begin(self.handle, tree_index, fm, st))
             for level in range(self.max_depth):
                 check(self.lib.cb_trainer_level_hist(self.handle, level, st))
-                torch.distributed.all_reduce(self._level_view(level), group=self.group)
+                with torch.cuda.nvtx.range("cobalt:allreduce"):
+                    torch.distributed.all_reduce(self._level_view(level), group=self.group)
                 check(self.lib.cb_trainer_level_split(self.handle, level, st))
             check(self.lib.cb_trainer_round_end(self.handle, st))
 

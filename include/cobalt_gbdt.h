@@ -112,6 +112,18 @@ int cb_hist_build(const uint8_t* bins, int64_t ldb, int n_features, const int32_
                   int64_t count, const int32_t* bin_ptr, int total_bins, int64_t* hist, void* workspace,
                   size_t workspace_bytes, void* stream);
 
+/* ---- K4 through the conflict-free kernel (the one the trainer launches at every level), on one node, standalone:
+ * bins in the placement of cb_plan_layout / cb_bin_pack_u8 (pos_feature i32 [ldb], groups, blocked as there; all device
+ * arrays), row_idx u32 [count] or NULL.  hist: int64 [total_bins][2] in natural feature order, overwritten; members of a
+ * one-hot group get bin 0 = (sum of the rows' pairs) - bin 1, as the trainer's split scan derives it.  Builds the
+ * shared-memory tables on the host from device copies of the placement and checks the launch's status, hence _sync.
+ * CB_ERR_UNSUPPORTED when the placement has no conflict-free image (then cb_hist_build is the path). */
+int cb_hist_build_cf_workspace_bytes(int64_t max_rows, int n_features, size_t* bytes);
+int cb_hist_build_cf_sync(const uint8_t* bins, int64_t n_rows, int64_t ldb, int blocked, const int32_t* pos_feature,
+                          const int32_t* grp_ptr, const int32_t* grp_feat, int n_groups, int n_features,
+                          const int32_t* gpair, const uint32_t* row_idx, int64_t count, const int32_t* bin_ptr,
+                          int total_bins, int64_t* hist, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- K9 sibling = parent - built (exact). */
 int cb_hist_subtract(const int64_t* parent, const int64_t* built, int64_t* sibling, int64_t n_values, void* stream);
 

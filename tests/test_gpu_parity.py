@@ -650,6 +650,37 @@ def test_onehot_groups_one_code_byte_bit_exact(ops):
     _assert_forest_equal(tr3.forest_numpy(), ref3["flat"])
 
 
+@pytest.mark.parametrize("group_onehot", [True, False])
+def test_conflict_free_histogram_kernel_standalone(ops, group_onehot):
+    """The kernel that is 60 % of a boosting round, called on its own through the C ABI with the row lists a trainer
+    would hand it -- all rows (root form), a gathered ragged subset, a tiny subset, one row, a subset larger than one
+    int32 chunk per CTA -- against the oracle's histogram, with and without one-hot group columns (one and two column
+    blocks)."""
+    from cobalt_smart_lender_ai_b200.binned import BinnedMatrix
+    from cobalt_smart_lender_ai_b200.synth import make_lending
+    n, f = 60000, 150
+    X, y, _ = make_lending(n, f, seed=17)
+    X, y = X.numpy(), y.numpy()
+    cuts, nc, mv = O.compute_cuts(X, 256)
+    bins = O.bin_matrix(X, cuts, nc)
+    bp = O.bin_ptr_of(nc)
+    rng = np.random.default_rng(3)
+    q = O.grad(rng.normal(size=n).astype(np.float32), y, None, 6.75, 14, 16)
+    bm = BinnedMatrix.from_dense(_dev(X), _dev(cuts), _dev(nc), group_onehot=group_onehot)
+    assert bm.cf and (bm.n_groups > 0) == group_onehot
+    qd, bpd, S = _dev(q), _dev(bp), int(bp[-1])
+    for rows in (None, np.sort(rng.permutation(n)[:23456]), np.sort(rng.permutation(n)[:300]), np.array([n - 1]),
+                 rng.permutation(n)[:40001]):                    # the last one unsorted: order must not matter
+        rd = None if rows is None else _dev(rows.astype(np.uint32).view(np.int32))
+        got = ops.hist_build_cf(bm, qd, rd, bpd, S).cpu().numpy()
+        want = O.hist(bins, f, q, None if rows is None else rows.astype(np.uint32), bp)
+        assert np.array_equal(got, want), None if rows is None else len(rows)
+    # more rows per CTA than one int32 partial may hold (16 352): 148 CTAs x 2 chunks needs > 2.4 M rows -- repeat rows
+    big = np.tile(np.arange(n, dtype=np.uint32), 45)[:2_500_000]
+    got = ops.hist_build_cf(bm, qd, _dev(big.view(np.int32)), bpd, S).cpu().numpy()
+    assert np.array_equal(got, O.hist(bins, f, q, big, bp))
+
+
 def test_onehot_detection_is_exact():
     """Grouping is decided on the data: one row where two indicators are both set, or one missing value, keeps a
     column out of every group; splits on grouped members (forced by the data) send exactly the member's rows right."""
