@@ -31,6 +31,11 @@
  *   - sigmoid uses the fixed operation sequence below (bit-reproducible on CPU and GPU).
  *   - subsample / colsample use their own counter-based hash (statistical parity only).
  *
+ * Threads (it is also bench.py's timed CPU baseline): cuts, binning, gradients, histogram build (per-thread private
+ * histograms kept between calls, slot-sliced merge), the split scan (contiguous feature ranges, combined in index order),
+ * the stable partition of large segments (chunk counts, prefix, write), totals and leaf updates all use OpenMP; results
+ * do not depend on the thread count (integer sums; same '>' tie-breaks in the same order).
+ *
  * Build: see oracle/Makefile (gcc -O2 -fopenmp -ffp-contract=off; no -ffast-math).
  */
 #include <math.h>
@@ -218,13 +223,44 @@ int orc_grad(const float* margin, const uint8_t* y, const float* w, int64_t n, f
 
 /* ------------------------------------------------------------------ R5: histogram -- */
 /* compact layout: slot = bin_ptr[f] + bin, hist[slot][2] int64; missing rows skipped */
+static int64_t** g_hist_loc = NULL;   /* per-thread private histograms, kept between calls */
+static int g_hist_loc_threads = 0;
+static size_t g_hist_loc_slots = 0;
+
 int orc_hist(const uint8_t* bins, int64_t ldb, int f, const int32_t* q, const uint32_t* row_idx,
              int64_t count, const int* bin_ptr, int64_t* hist) {
   int S = bin_ptr[f];
-  memset(hist, 0, sizeof(int64_t) * 2 * (size_t)S);
+  int nt = omp_get_max_threads();
+  if (count < 8192 || nt == 1) {                 /* small node: one thread, straight into the output */
+    memset(hist, 0, sizeof(int64_t) * 2 * (size_t)S);
+    for (int64_t i = 0; i < count; ++i) {
+      int64_t r = row_idx ? (int64_t)row_idx[i] : i;
+      int64_t g = q[2 * r], h = q[2 * r + 1];
+      const uint8_t* b = bins + r * ldb;
+      for (int j = 0; j < f; ++j) {
+        if (b[j] == ORC_MISSING) continue;
+        int s = bin_ptr[j] + b[j];
+        hist[2 * s] += g; hist[2 * s + 1] += h;
+      }
+    }
+    return 0;
+  }
+  if (nt > g_hist_loc_threads || (size_t)S > g_hist_loc_slots) {
+    for (int k = 0; k < g_hist_loc_threads; ++k) free(g_hist_loc[k]);
+    free(g_hist_loc);
+    g_hist_loc = (int64_t**)malloc(sizeof(int64_t*) * (size_t)nt);
+    if (!g_hist_loc) { g_hist_loc_threads = 0; return -1; }
+    for (int k = 0; k < nt; ++k) g_hist_loc[k] = (int64_t*)malloc(sizeof(int64_t) * 2 * (size_t)S);
+    g_hist_loc_threads = nt; g_hist_loc_slots = (size_t)S;
+  }
+  int used = 0;
 #pragma omp parallel
   {
-    int64_t* loc = (int64_t*)calloc((size_t)S * 2, sizeof(int64_t));
+    int tid = omp_get_thread_num();
+#pragma omp single
+    used = omp_get_num_threads();
+    int64_t* loc = g_hist_loc[tid];
+    memset(loc, 0, sizeof(int64_t) * 2 * (size_t)S);
 #pragma omp for schedule(static)
     for (int64_t i = 0; i < count; ++i) {
       int64_t r = row_idx ? (int64_t)row_idx[i] : i;
@@ -236,9 +272,13 @@ int orc_hist(const uint8_t* bins, int64_t ldb, int f, const int32_t* q, const ui
         loc[2 * s] += g; loc[2 * s + 1] += h;
       }
     }
-#pragma omp critical
-    for (int s = 0; s < 2 * S; ++s) hist[s] += loc[s];
-    free(loc);
+    /* merge: every thread sums a slice of the slots over all private copies (integer sums: order free) */
+#pragma omp for schedule(static)
+    for (int s = 0; s < 2 * S; ++s) {
+      int64_t a = 0;
+      for (int k = 0; k < used; ++k) a += g_hist_loc[k][s];
+      hist[s] = a;
+    }
   }
   return 0;
 }
@@ -283,14 +323,12 @@ double orc_calc_weight(double G, double H, float lambda, float alpha, float mcw)
   return calc_weight(G, H, &p);
 }
 
-/* hist: node's compact histogram; Gt/Ht: node totals; feature_mask may be NULL */
-int orc_scan(const int64_t* hist, const int* bin_ptr, int f, const float* cuts, const float* min_vals,
-             int64_t Gt, int64_t Ht, const orc_tparams* p, const uint8_t* feature_mask,
-             orc_split* out) {
-  double ig = ldexp(1.0, -p->sg), ih = ldexp(1.0, -p->sh);
-  float root_gain = (float)calc_gain((double)Gt * ig, (double)Ht * ih, p);
-  orc_split best; memset(&best, 0, sizeof best); best.feature = -1; best.loss_chg = 0.0f;
-  for (int j = 0; j < f; ++j) {
+/* features [j0, j1) of one node, in index order; *pbest must come in initialised (feature -1, loss_chg 0) */
+static void scan_range(const int64_t* hist, const int* bin_ptr, int j0, int j1, const float* cuts, const float* min_vals,
+                       int64_t Gt, int64_t Ht, const orc_tparams* p, const uint8_t* feature_mask, double ig, double ih,
+                       float root_gain, orc_split* pbest) {
+  orc_split best = *pbest;
+  for (int j = j0; j < j1; ++j) {
     if (feature_mask && !feature_mask[j]) continue;
     int nb = bin_ptr[j + 1] - bin_ptr[j];
     const int64_t* hj = hist + 2 * (size_t)bin_ptr[j];
@@ -327,6 +365,33 @@ int orc_scan(const int64_t* hist, const int* bin_ptr, int f, const float* cuts, 
       }
     }
   }
+  *pbest = best;
+}
+
+/* hist: node's compact histogram; Gt/Ht: node totals; feature_mask may be NULL */
+int orc_scan(const int64_t* hist, const int* bin_ptr, int f, const float* cuts, const float* min_vals,
+             int64_t Gt, int64_t Ht, const orc_tparams* p, const uint8_t* feature_mask,
+             orc_split* out) {
+  double ig = ldexp(1.0, -p->sg), ih = ldexp(1.0, -p->sh);
+  float root_gain = (float)calc_gain((double)Gt * ig, (double)Ht * ih, p);
+  orc_split best; memset(&best, 0, sizeof best); best.feature = -1; best.loss_chg = 0.0f;
+  int nt = omp_get_max_threads();
+  if (nt > 64) nt = 64;
+  if (f < 32 || nt == 1) {
+    scan_range(hist, bin_ptr, 0, f, cuts, min_vals, Gt, Ht, p, feature_mask, ig, ih, root_gain, &best);
+  } else {
+    /* contiguous feature ranges per thread, combined in range order with the same strict '>' as the serial scan:
+       the lowest feature index still wins ties */
+    orc_split part[64];
+#pragma omp parallel for schedule(static, 1) num_threads(nt)
+    for (int k = 0; k < nt; ++k) {
+      memset(&part[k], 0, sizeof part[k]); part[k].feature = -1; part[k].loss_chg = 0.0f;
+      scan_range(hist, bin_ptr, (int)((long long)f * k / nt), (int)((long long)f * (k + 1) / nt), cuts, min_vals, Gt, Ht, p,
+                 feature_mask, ig, ih, root_gain, &part[k]);
+    }
+    for (int k = 0; k < nt; ++k)
+      if (part[k].feature >= 0 && part[k].loss_chg > best.loss_chg) best = part[k];
+  }
   *out = best;
   return 0;
 }
@@ -335,17 +400,45 @@ int orc_scan(const int64_t* hist, const int* bin_ptr, int f, const float* cuts, 
 /* stable split of seg[0..count) into out (lefts first); returns number of lefts */
 int64_t orc_partition(const uint8_t* bins, int64_t ldb, const uint32_t* seg, int64_t count,
                       int feature, int split_bin, int default_left, uint32_t* out) {
-  int64_t nl = 0;
-  for (int64_t i = 0; i < count; ++i) {
-    uint8_t c = bins[(int64_t)seg[i] * ldb + feature];
-    int left = c == ORC_MISSING ? default_left : ((int)c <= split_bin);
-    nl += left;
+  int nt = omp_get_max_threads();
+  if (count < 65536 || nt == 1) {
+    int64_t nl = 0;
+    for (int64_t i = 0; i < count; ++i) {
+      uint8_t c = bins[(int64_t)seg[i] * ldb + feature];
+      int left = c == ORC_MISSING ? default_left : ((int)c <= split_bin);
+      nl += left;
+    }
+    int64_t a = 0, b = nl;
+    for (int64_t i = 0; i < count; ++i) {
+      uint8_t c = bins[(int64_t)seg[i] * ldb + feature];
+      int left = c == ORC_MISSING ? default_left : ((int)c <= split_bin);
+      if (left) out[a++] = seg[i]; else out[b++] = seg[i];
+    }
+    return nl;
   }
-  int64_t a = 0, b = nl;
-  for (int64_t i = 0; i < count; ++i) {
-    uint8_t c = bins[(int64_t)seg[i] * ldb + feature];
-    int left = c == ORC_MISSING ? default_left : ((int)c <= split_bin);
-    if (left) out[a++] = seg[i]; else out[b++] = seg[i];
+  /* large segment: contiguous chunk per thread, count, exclusive prefix over the chunks, write -- still stable */
+  int64_t cnt[256];
+  if (nt > 256) nt = 256;
+  int64_t per = (count + nt - 1) / nt, nl = 0;
+#pragma omp parallel for schedule(static, 1) num_threads(nt)
+  for (int k = 0; k < nt; ++k) {
+    int64_t b0 = k * per, b1 = b0 + per < count ? b0 + per : count, c0 = 0;
+    for (int64_t i = b0; i < b1; ++i) {
+      uint8_t c = bins[(int64_t)seg[i] * ldb + feature];
+      c0 += c == ORC_MISSING ? default_left : ((int)c <= split_bin);
+    }
+    cnt[k] = c0;
+  }
+  for (int k = 0; k < nt; ++k) { int64_t c0 = cnt[k]; cnt[k] = nl; nl += c0; }
+#pragma omp parallel for schedule(static, 1) num_threads(nt)
+  for (int k = 0; k < nt; ++k) {
+    int64_t b0 = k * per, b1 = b0 + per < count ? b0 + per : count;
+    int64_t a = cnt[k], b = nl + (b0 < count ? b0 : count) - cnt[k];
+    for (int64_t i = b0; i < b1; ++i) {
+      uint8_t c = bins[(int64_t)seg[i] * ldb + feature];
+      int left = c == ORC_MISSING ? default_left : ((int)c <= split_bin);
+      if (left) out[a++] = seg[i]; else out[b++] = seg[i];
+    }
   }
   return nl;
 }
@@ -387,6 +480,7 @@ int orc_train(const uint8_t* bins, int64_t ldb, int64_t n, int f, const int* bin
     const uint8_t* fmask = feature_masks ? feature_masks + (size_t)t * f : NULL;
     orc_grad(margin, y, w, n, spw, p->sg, p->sh, keep_thresh, seed, (uint32_t)(tree_offset + t), 0, q);
     int64_t G = 0, H = 0;
+#pragma omp parallel for schedule(static) reduction(+ : G, H)
     for (int64_t i = 0; i < n; ++i) { G += q[2 * i]; H += q[2 * i + 1]; ridx[i] = (uint32_t)i; }
     for (int k = 0; k < max_nodes; ++k) {
       fo->left[base + k] = -1; fo->right[base + k] = -1; fo->parent[base + k] = 2147483647;
@@ -416,7 +510,8 @@ int orc_train(const uint8_t* bins, int64_t ldb, int64_t n, int f, const int* bin
           fo->split_cond[base + nd.nid] = leaf;
           fo->base_weight[base + nd.nid] = leaf;
           leaf_of_node[nd.nid] = leaf;
-          for (int64_t i = 0; i < nd.count; ++i) margin[ridx[nd.begin + i]] += leaf;
+#pragma omp parallel for schedule(static) if (nd.count > 32768)
+          for (int64_t i = 0; i < nd.count; ++i) margin[ridx[nd.begin + i]] += leaf;   /* rows are distinct: no race */
           continue;
         }
         int L = n_nodes, R = n_nodes + 1; n_nodes += 2;
