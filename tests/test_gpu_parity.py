@@ -753,6 +753,48 @@ def test_full_size_properties(ops):
     assert np.array_equal(np.sort(rows), np.arange(n, dtype=np.uint32))
 
 
+def test_c3_size_properties(ops):
+    """BASELINE configs[3] size on one GPU's share and beyond (20M x 150, depth 8): the oracle cannot run this in
+    seconds, so the size-independent properties stand in -- exact histogram additivity down to depth 8, margin replay
+    through the scoring kernel bit for bit, the row order a permutation with ascending leaf segments."""
+    from cobalt_smart_lender_ai_b200.binned import BinnedMatrix
+    from cobalt_smart_lender_ai_b200.booster import Booster
+    from cobalt_smart_lender_ai_b200.synth import make_lending
+    from cobalt_smart_lender_ai_b200.trainer import GpuTrainer
+    free, _total = torch.cuda.mem_get_info()
+    if free < 90e9:
+        pytest.skip("needs ~90 GB of free device memory")
+    n, f, D = 20_000_000, 150, 8
+    X = torch.empty((n, f), dtype=torch.float32, device="cuda")
+    y = torch.empty(n, dtype=torch.uint8, device="cuda")
+    for b in range(0, n, 2_000_000):
+        Xc, yc, _ = make_lending(2_000_000, f, row_offset=b, device="cuda")
+        X[b:b + 2_000_000], y[b:b + 2_000_000] = Xc, yc
+    del Xc, yc
+    cuts, n_cuts, min_vals = ops.sketch_cuts(X, 256)
+    bm = BinnedMatrix.from_dense(X, cuts, n_cuts)
+    bp = ops.bin_ptr_of(n_cuts)
+    spw = float(((y == 0).sum() / (y == 1).sum()).item())
+    sg, sh = ops.quant_shifts(spw)
+    tr = GpuTrainer(bm, y, None, f, bp, cuts, min_vals, max_depth=D, eta=0.3, scale_pos_weight=spw, sg=sg, sh=sh,
+                    max_trees=2, group=False)
+    tr.boost(2)
+    fo = tr.forest_numpy()
+    a = int(fo["tree_offsets"][1])
+    L, R = fo["left"][a:], fo["right"][a:]
+    checked = 0
+    for nid in range(len(L)):
+        if L[nid] >= 0 and R[nid] < (1 << D) - 1:                 # children with a histogram slot (depth < 8)
+            assert torch.equal(tr.node_hist(nid), tr.node_hist(int(L[nid])) + tr.node_hist(int(R[nid])))
+            checked += 1
+    assert checked >= 100
+    m = Booster(fo, f, None, 0.5).predict_device(X, output_margin=True)
+    assert torch.equal(m.view(torch.int32), tr.margin.view(torch.int32))
+    rows = tr.row_order().cpu().numpy().view(np.uint32)
+    assert np.array_equal(np.sort(rows), np.arange(n, dtype=np.uint32))
+    tr.close()
+
+
 def test_scoring_service_on_gpu(ops, fixture_forest, tmp_path):
     """src/api path end to end: the reference's shipped forest served through the FastAPI mirror
     (/predict_bulk_csv -> predict_proba_df -> cb_predict_heap), model written and re-read as a .ubj file."""
