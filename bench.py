@@ -311,6 +311,10 @@ def run_ours(args):
     n_rows = args.rows
     r0, r1 = parallel.shard_rows(n_rows, rank, world)
     X, y, _names = make_lending(r1 - r0, N_FEAT, row_offset=r0, device=dev)
+    if args.schema == "continuous":       # every column continuous: 150 x 255 bins do not fit one shared-memory image,
+        g = torch.Generator(device=dev).manual_seed(1234 + rank)        # so this measures the tiled fallback kernel
+        X = X + 1e-3 * torch.randn(X.shape, generator=g, device=dev)
+        X[X != X] = 0.0
     n_pos = torch.tensor([float((y == 1).sum())], dtype=torch.float64, device=dev)
     if world > 1:
         torch.distributed.all_reduce(n_pos)
@@ -664,10 +668,15 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-scoring", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--schema", default="lending", choices=["lending", "continuous"],
+                    help="continuous: jitter every column so that all 150 have 255 bins (measures the tiled fallback histogram kernel)")
     ap.add_argument("--no-groups", action="store_true", help="one byte per feature (no one-hot group columns)")
     ap.add_argument("--no-hgb", action="store_true", help="skip the sklearn HistGradientBoosting baseline and config C0")
     args = ap.parse_args()
-    if args.depth != DEPTH or args.rows != N_ROWS:
+    if args.schema != "lending":
+        DEPTH = args.depth
+        WORKLOAD = f"{args.rows / 1e6:g}M x {N_FEAT} all-continuous columns (150 x 255 bins), depth {args.depth}: NOT a BASELINE config, fallback-kernel measurement"
+    elif args.depth != DEPTH or args.rows != N_ROWS:
         DEPTH = args.depth
         WORKLOAD = (f"synthetic Lending-Club schema {args.rows / 1e6:g}M x {N_FEAT}, 256 bins, depth {DEPTH}"
                     + (" (BASELINE.json configs[3])" if (args.rows, DEPTH) == (20_000_000, 8) else ""))

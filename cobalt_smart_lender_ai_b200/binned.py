@@ -98,6 +98,11 @@ class BinnedMatrix:
                 continue                                   # grouped placement does not fit: plain columns
             groups = attempt
             break
+        if not cf:
+            import warnings
+            warnings.warn(f"cobalt: {int(n_cuts.sum().item())} bins over {f} columns have no conflict-free shared-memory "
+                          "image (about 24 000 bin slots fit); the tiled histogram kernel will run, several times slower per "
+                          "row -- consider a smaller max_bin", RuntimeWarning, stacklevel=2)
         dev = X.device
         pos = torch.from_numpy(pos_np).to(dev)
         gp, gf = ops.group_arrays(groups)
