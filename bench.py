@@ -154,6 +154,15 @@ def _timed(fn, world, dev):
     return float(ms.item())
 
 
+def _xgboost_probe() -> str:
+    """BASELINE.md section 3, baseline 1: the reference's own CPU path is the xgboost package -- probed at run start."""
+    try:
+        import xgboost  # noqa: F401
+        return f"importable ({xgboost.__version__}) -- not used: the timed CPU arm is the oracle port, see DESIGN.md section 6"
+    except Exception as e:
+        return f"unavailable on this box ({type(e).__name__})"
+
+
 def _config(n_rows, steps, warmup, world):
     """the `config` object: the workload, identical in both arms (the driver compares them)"""
     return {"workload": WORKLOAD, "rows": n_rows, "features": N_FEAT, "max_bin": 256, "max_depth": DEPTH,
@@ -588,6 +597,7 @@ def run_ours(args):
                 "data": "synthetic", "config": _config(n_rows, args.steps, args.warmup, world),
                 "detail": {"total_bins": S, "effective_bins_per_feature": 255, "layout": layout, "cuda_graph": graph_state,
                            "exchange": ("NVLink peer memory inside the split scan" if peer_mode else "NCCL allreduce") if world > 1 else None},
+                "reference_xgboost": _xgboost_probe(),
                 "roofline": roofline, "cpu_baseline": cpu, "cpu_baseline_hgb": hgb, "parity": parity, "c0": c0,
                 "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clk.summary(), "scoring": scoring, "prep_ms": round(t_prep, 2), "train_auc_200k": auc}
@@ -641,7 +651,8 @@ def run_reference(args):
             "data": "synthetic", "config": _config(args.rows, args.steps, args.warmup, args.gpus),
             "cpu_baseline": {"value": round(val, 3), "unit": "rounds/s", "cores": O.num_threads(), "kind": "port", "sample": sample},
             "e2e": {"value": round(val, 3), "unit": "rounds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "raw_rounds_per_s_on_sample": round(args.steps / dt, 3), "prep_seconds": round(t_prep, 2)}
+            "raw_rounds_per_s_on_sample": round(args.steps / dt, 3), "prep_seconds": round(t_prep, 2),
+            "reference_xgboost": _xgboost_probe()}
     print(json.dumps(line), file=_OUT, flush=True)
 
 
