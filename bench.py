@@ -158,9 +158,26 @@ def _xgboost_probe() -> str:
     """BASELINE.md section 3, baseline 1: the reference's own CPU path is the xgboost package -- probed at run start."""
     try:
         import xgboost  # noqa: F401
-        return f"importable ({xgboost.__version__}) -- not used: the timed CPU arm is the oracle port, see DESIGN.md section 6"
+        return f"importable ({xgboost.__version__})"
     except Exception as e:
         return f"unavailable on this box ({type(e).__name__})"
+
+
+def _xgboost_rounds_per_s(X, y, spw, steps, depth):
+    """The reference's real CPU path, if the box has it: rounds/s of xgboost `hist` between a 2-round and a
+    (2 + steps)-round fit (its sketch and binning are not charged to the rounds).  None when xgboost is absent or fails."""
+    try:
+        import xgboost
+        kw = dict(tree_method="hist", max_bin=256, max_depth=depth, learning_rate=ETA, scale_pos_weight=spw,
+                  n_jobs=os.cpu_count(), eval_metric="logloss")
+        ts = []
+        for k in (2, 2 + steps):
+            t0 = time.perf_counter()
+            xgboost.XGBClassifier(n_estimators=k, **kw).fit(X, y)
+            ts.append(time.perf_counter() - t0)
+        return steps / max(ts[1] - ts[0], 1e-9)
+    except Exception:
+        return None
 
 
 def _config(n_rows, steps, warmup, world):
@@ -639,7 +656,13 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     scale = n / args.rows
     val = args.steps / dt * scale
-    if n == args.rows:
+    xgb_val = _xgboost_rounds_per_s(X, y, spw, args.steps, DEPTH)
+    kind = "port"
+    if xgb_val is not None:                   # the box has the reference's own implementation: that is the reference arm
+        val, kind, scale = xgb_val * scale, "reference", scale
+    if xgb_val is not None:
+        sample = (f"xgboost hist, n_jobs={os.cpu_count()}, {n} x {N_FEAT}: ({2 + args.steps}-round fit - 2-round fit) / {args.steps}")
+    elif n == args.rows:
         sample = (f"every step is one round on the full {n} x {N_FEAT} binned matrix; oracle/gbdt_oracle.c with OpenMP on "
                   f"{O.num_threads()} threads; reference xgboost unavailable on this box")
     else:
@@ -649,7 +672,7 @@ def run_reference(args):
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3 / scale, 2),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int64 fixed-point (f32 gradients, f64 gains)",
             "data": "synthetic", "config": _config(args.rows, args.steps, args.warmup, args.gpus),
-            "cpu_baseline": {"value": round(val, 3), "unit": "rounds/s", "cores": O.num_threads(), "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": round(val, 3), "unit": "rounds/s", "cores": O.num_threads(), "kind": kind, "sample": sample},
             "e2e": {"value": round(val, 3), "unit": "rounds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "raw_rounds_per_s_on_sample": round(args.steps / dt, 3), "prep_seconds": round(t_prep, 2),
             "reference_xgboost": _xgboost_probe()}
