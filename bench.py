@@ -587,6 +587,7 @@ def run_ours(args):
     if rank == 0 and bins_cpu is not None:
         from oracle import oracle as O
         O.set_threads(os.cpu_count() or 1)
+        torch.set_num_threads(1)          # torch ships its own OpenMP runtime: keep its pool out of the timed port's way
         tp = O.TreeParams(eta=float(np.float32(ETA)), max_depth=DEPTH, sg=sg, sh=sh)
         margin = np.zeros(len(y_cpu), np.float32)
         bp = O.bin_ptr_of(nc_cpu)
@@ -641,6 +642,7 @@ def run_reference(args):
     dev = "cuda" if torch.cuda.is_available() else "cpu"
     X, y, _ = make_lending(n, N_FEAT, device=dev)
     X, y = X.cpu().numpy(), y.cpu().numpy()
+    torch.set_num_threads(1)              # torch ships its own OpenMP runtime: keep its pool out of the timed port's way
     spw = float((y == 0).sum() / (y == 1).sum())
     t0 = time.perf_counter()
     cuts, nc, mv = O.compute_cuts(X, 256)
