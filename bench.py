@@ -587,7 +587,6 @@ def run_ours(args):
     if rank == 0 and bins_cpu is not None:
         from oracle import oracle as O
         O.set_threads(os.cpu_count() or 1)
-        torch.set_num_threads(1)          # torch ships its own OpenMP runtime: keep its pool out of the timed port's way
         tp = O.TreeParams(eta=float(np.float32(ETA)), max_depth=DEPTH, sg=sg, sh=sh)
         margin = np.zeros(len(y_cpu), np.float32)
         bp = O.bin_ptr_of(nc_cpu)
@@ -642,7 +641,12 @@ def run_reference(args):
     dev = "cuda" if torch.cuda.is_available() else "cpu"
     X, y, _ = make_lending(n, N_FEAT, device=dev)
     X, y = X.cpu().numpy(), y.cpu().numpy()
-    torch.set_num_threads(1)              # torch ships its own OpenMP runtime: keep its pool out of the timed port's way
+    if dev == "cpu":
+        # no GPU (this arm's contract test): the data was generated by torch's CPU thread pool, whose OpenMP runtime is
+        # not the port's -- two pools fighting over the cores slowed the port 8x.  Park torch's, then size the port's
+        # again (where the two share one runtime the first call would otherwise have set the port to one thread too).
+        torch.set_num_threads(1)
+        O.set_threads(os.cpu_count() or 1)
     spw = float((y == 0).sum() / (y == 1).sum())
     t0 = time.perf_counter()
     cuts, nc, mv = O.compute_cuts(X, 256)
