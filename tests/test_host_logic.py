@@ -345,3 +345,52 @@ def test_load_model_never_unpickles_a_foreign_file(tmp_path, fixture_forest):
     c.write_bytes(pickle.dumps({"x": Evil()}))
     with pytest.raises(Exception):
         load_model(c)          # joblib.load is reached only for payload-free files; a foreign object is refused
+
+
+def test_row_stride_group_arrays_and_code_unpacking():
+    """Host logic of the binned-matrix layer: row strides never let a column block's row straddle a 128-byte line;
+    group arrays are CSR; natural_codes() undoes placement, column blocks and one-hot packing."""
+    import torch
+
+    from cobalt_smart_lender_ai_b200 import ops
+    from cobalt_smart_lender_ai_b200.binned import BinnedMatrix
+    for n_cols in range(1, 400):
+        ldb = ops.padded_ldb(n_cols)
+        last = ldb - 128 * ((ldb - 1) // 128)
+        assert ldb >= n_cols and ldb % 4 == 0 and last & (last - 1) == 0 and last >= 16, (n_cols, ldb)
+    assert [ops.padded_ldb(k) for k in (112, 128, 150)] == [128, 128, 160]
+    ptr, feat = ops.group_arrays([[3, 5, 9], [1, 2]])
+    assert ptr.tolist() == [0, 3, 5] and feat.tolist() == [3, 5, 9, 1, 2] and ops.group_arrays([]) == (None, None)
+    # 6 features: 0 and 4 plain, group A = [1, 2, 3] in one byte, feature 5 plain; placement scrambled, ldb 16
+    rng = np.random.default_rng(0)
+    n = 50
+    nat = np.zeros((n, 6), np.uint8)
+    nat[:, 0] = rng.integers(0, 200, n)
+    nat[:, 4] = rng.integers(0, 9, n)
+    nat[:, 5] = np.where(rng.random(n) < 0.2, 255, rng.integers(0, 3, n))
+    which = rng.integers(0, 4, n)                                  # 0: none of the group set
+    for m in range(3):
+        nat[:, 1 + m] = which == m + 1
+    pos = np.full(16, -1, np.int32)
+    pos[[7, 2, 9, 12]] = [0, 4, -2, 5]                            # byte 9 holds group 0
+    b = np.full((n, 16), 255, np.uint8)
+    b[:, 7], b[:, 2], b[:, 9], b[:, 12] = nat[:, 0], nat[:, 4], which.astype(np.uint8), nat[:, 5]
+    bm = BinnedMatrix(torch.from_numpy(b), None, None, pos, None, None, [[1, 2, 3]], False, True, n, 6, 16)
+    assert np.array_equal(bm.natural_codes(), nat)
+    # block-major storage of a 160-byte row: block 0 = [n][128] then block 1 = [n][32]
+    wide = rng.integers(0, 255, (n, 160)).astype(np.uint8)
+    stored = np.concatenate([wide[:, :128].reshape(-1), wide[:, 128:].reshape(-1)]).reshape(n, 160)
+    bm2 = BinnedMatrix(torch.from_numpy(stored), None, None, np.arange(160, dtype=np.int32), None, None, [], True, True, n, 160, 160)
+    assert np.array_equal(bm2.natural_codes(), wide)
+
+
+def test_local_only_hides_the_process_group():
+    """parallel.local_only(): inside it the path behaves as single-process whatever torch.distributed says (nesting ok)."""
+    from cobalt_smart_lender_ai_b200 import parallel
+    assert parallel.world_size() == 1 and parallel._dist() is None
+    with parallel.local_only():
+        with parallel.local_only():
+            assert parallel._LOCAL_ONLY == 2 and parallel.world_size() == 1
+        assert parallel._LOCAL_ONLY == 1
+    assert parallel._LOCAL_ONLY == 0
+    assert parallel.global_stats(3.0, 5.0, 2.0, 10) == (3.0, 5.0, 2.0, 0)
